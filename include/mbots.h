@@ -1,0 +1,173 @@
+/* mbots.h -- C-ABI of the B200-native madrona-bots step library (libmbots.so).
+ *
+ * This is the drop-in boundary for the per-step hot path of llGuy/madrona-bots:
+ * every entry point replaces one member of the reference's `Manager`
+ * (src/entry/mgr.hpp:28-62, src/entry/mgr.cpp) that the nanobind module
+ * `madrona_bots.SimManager` binds (src/entry/entry.cpp:16-44).
+ *
+ * Conventions
+ *   - plain C, no exceptions cross the boundary; every call returns 0 on
+ *     success and a negative MBOTS_E* code otherwise; mbots_last_error() gives
+ *     the message of the last failure on the calling thread.
+ *   - the library OWNS all device memory of a handle; pointers returned by
+ *     mbots_tensor() stay valid until the next mbots_step*() call on that
+ *     handle (row-indexed exports are double-buffered: a step re-packs every
+ *     agent's row, exactly as the reference's per-step archetype sorts do, and
+ *     the caller is already required to re-fetch tensors every step because
+ *     their leading dimension changes -- src/entry/mgr.cpp:199-422).
+ *   - one host thread per handle; calls on a handle are serialised by the
+ *     caller. One handle per GPU per process is the intended use.
+ *   - `stream` arguments are CUDA stream handles (cudaStream_t / CUstream)
+ *     passed as void*; NULL = the legacy default stream.
+ */
+#ifndef MBOTS_H
+#define MBOTS_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct mbots_sim mbots_sim;
+
+/* Same order and meaning as the reference's ExportID (src/sim/sim.hpp:18-55). */
+enum mbots_export_id {
+    MBOTS_EXPORT_RESET = 0,            /* int32  (numWorlds, 1)  accepted, ignored (U10) */
+    MBOTS_EXPORT_ACTION,               /* int32  (A, 6)   caller writes  */
+    MBOTS_EXPORT_PREV_ACTION,          /* int32  (A, 6) */
+    MBOTS_EXPORT_HIDDEN_STATE,         /* float32 (A, 16) caller writes  */
+    MBOTS_EXPORT_PREV_HIDDEN_STATE,    /* float32 (A, 16) */
+    MBOTS_EXPORT_REWARD,               /* float32 (A, 1) */
+    MBOTS_EXPORT_PREV_REWARD,          /* float32 (A, 1) */
+    MBOTS_EXPORT_DONE,                 /* int32  (A, 1)   always 0 (U10), agent order */
+    MBOTS_EXPORT_POSITION,             /* float32 (A, 2) */
+    MBOTS_EXPORT_PREV_POSITION,        /* float32 (A, 2) */
+    MBOTS_EXPORT_HEALTH,               /* float32 (A, 1)  numeric value (U4) */
+    MBOTS_EXPORT_PREV_HEALTH,          /* float32 (A, 1) */
+    MBOTS_EXPORT_SURROUNDING,          /* float32 (A, 2) */
+    MBOTS_EXPORT_PREV_SURROUNDING,     /* float32 (A, 2) */
+    MBOTS_EXPORT_SENSOR_SEMANTIC,      /* int8   (A, 32) */
+    MBOTS_EXPORT_SENSOR_DEPTH,         /* uint8  (A, 32) */
+    MBOTS_EXPORT_PREV_SENSOR_SEMANTIC, /* int8   (A, 32) */
+    MBOTS_EXPORT_PREV_SENSOR_DEPTH,    /* uint8  (A, 32) */
+    MBOTS_EXPORT_STATS,                /* int32  (A, 4) */
+    MBOTS_EXPORT_PREV_STATS,           /* int32  (A, 4) */
+    MBOTS_EXPORT_SENSOR_INDEX,         /* int32  (A, 1)  agent (world, slot) order -> obs row */
+    MBOTS_EXPORT_SPECIES_COUNT,        /* int32  (numWorlds, 4) */
+    MBOTS_NUM_EXPORTS,
+
+    /* Not part of the reference: internal state exposed for parity audits.
+     * "agent order" = (world, slot), the order of the reference's Agent table
+     * after its per-step world sort (src/sim/sim.cpp:1129-1130). */
+    MBOTS_DEBUG_WORLD_COUNT = 100,     /* int32  (numWorlds, 1) live agents per world */
+    MBOTS_DEBUG_WORLD_OFFSET,          /* int32  (numWorlds, 1) exclusive scan of the above */
+    MBOTS_DEBUG_RNG_COUNT,             /* int32  (numWorlds, 1) draws consumed so far */
+    MBOTS_DEBUG_NUM_FOOD,              /* int32  (numWorlds, 1) */
+    MBOTS_DEBUG_FOOD,                  /* uint8  (numWorlds*48, 8): cells[5] (x<<4|y), mask, 0, 0 */
+    MBOTS_DEBUG_POSE,                  /* float32 (A, 4) x, y, quat.w, quat.z; agent order */
+    MBOTS_DEBUG_AGENT_HEALTH,          /* int32  (A, 1) agent order */
+    MBOTS_DEBUG_AGENT_SPECIES,         /* int32  (A, 1) agent order */
+    MBOTS_DEBUG_AGENT_TARGET,          /* int32  (A, 1) finder hit as slot in own world, -1 none */
+    MBOTS_DEBUG_ROW_BASE               /* int32  (numWorlds, 4) first obs row of (world, species) */
+};
+
+enum mbots_dtype {
+    MBOTS_I32 = 0,
+    MBOTS_F32 = 1,
+    MBOTS_I8 = 2,
+    MBOTS_U8 = 3
+};
+
+enum mbots_error {
+    MBOTS_OK = 0,
+    MBOTS_EINVAL = -1,   /* bad argument */
+    MBOTS_ECUDA = -2,    /* a CUDA call failed */
+    MBOTS_ENOMEM = -3,
+    MBOTS_ESTATE = -4    /* call not valid in this state */
+};
+
+/* Sizes fixed by the reference (src/entry/mgr.cpp:104-113,132-133). */
+#define MBOTS_NUM_SPECIES 4
+#define MBOTS_HIDDEN_DIM 16
+#define MBOTS_SENSOR_SIZE 32
+#define MBOTS_CHUNKS_X 8
+#define MBOTS_CHUNKS_Y 6
+#define MBOTS_NUM_CHUNKS 48
+#define MBOTS_FOOD_CAP 30
+#define MBOTS_NUM_STATS 16
+
+typedef struct mbots_config {
+    int32_t gpu_id;                    /* Manager::Config::gpuID */
+    uint32_t num_worlds;               /* Manager::Config::numWorlds (worlds owned by THIS handle) */
+    uint32_t rand_seed;                /* Manager::Config::randSeed */
+    uint32_t init_num_agents_per_world;/* Manager::Config::initNumAgentsPerWorld */
+    /* Extensions (0 = default): */
+    uint32_t max_agents_per_world;     /* per-world slot capacity; default max(128, 4*init) rounded to 32 */
+    uint32_t world_id_offset;          /* global id of local world 0 (multi-GPU sharding); RNG streams
+                                          are keyed on the GLOBAL id so results are shard-invariant */
+} mbots_config;
+
+/* Manager::Manager (src/entry/mgr.cpp:176-179 -> Impl::make :98-172) as bound by
+ * SimManager.__init__ (src/entry/entry.cpp:17-32). */
+int mbots_create(int32_t gpu_id, uint32_t num_worlds, uint32_t rand_seed,
+                 uint32_t init_num_agents_per_world, mbots_sim **out);
+int mbots_create_ex(const mbots_config *cfg, mbots_sim **out);
+int mbots_destroy(mbots_sim *sim);
+
+/* Manager::step (src/entry/mgr.cpp:189-192 -> Impl::step :51-63): step graph + sensor
+ * graph, then blocks until the device is done (cuda_exec.cpp:2977-2981). */
+int mbots_step(mbots_sim *sim, void *stream);
+/* Same work, enqueued only (no host synchronisation). mbots_num_agents() and the
+ * dims reported by mbots_tensor() are stale until mbots_sync(). */
+int mbots_step_async(mbots_sim *sim, void *stream);
+int mbots_sync(mbots_sim *sim, void *stream);
+
+/* Manager::shiftObservations (src/entry/mgr.cpp:194-197). Blocking. */
+int mbots_shift_observations(mbots_sim *sim, void *stream);
+int mbots_shift_observations_async(mbots_sim *sim, void *stream);
+
+/* SimBridge::totalNumAgents (src/sim/sim.hpp:73-77; written by bridgeSyncSystem,
+ * src/sim/sim.cpp:985-999). */
+int mbots_num_agents(mbots_sim *sim, uint32_t *out);
+
+/* Manager::*Tensor (src/entry/mgr.cpp:199-422 -> Impl::exportTensor :70-76): device
+ * pointer, dims and dtype of one export. `id` is an mbots_export_id. */
+int mbots_tensor(mbots_sim *sim, int32_t id, void **dev_ptr, int64_t dims[2], int32_t *dtype);
+
+/* Manager::setAction (src/entry/mgr.cpp:251-272): write one row of the action export. */
+int mbots_set_action(mbots_sim *sim, uint32_t agent_idx, int32_t forward, int32_t backward,
+                     int32_t rotate_left, int32_t rotate_right, int32_t shoot, int32_t breed);
+
+/* Manager::agentOffsetForWorld (src/entry/mgr.cpp:274-277). */
+int mbots_agent_offset_for_world(mbots_sim *sim, uint32_t world_idx, uint32_t *out);
+
+/* Host-buffer helpers for callers that keep their data on the host (bench e2e):
+ * copy `bytes` between a host buffer and the start of export `id` on `stream`. */
+int mbots_copy_from_host(mbots_sim *sim, int32_t id, const void *host, uint64_t bytes, void *stream);
+int mbots_copy_to_host(mbots_sim *sim, int32_t id, void *host, uint64_t bytes, void *stream);
+
+/* Cumulative episode statistics of this handle since creation, as 16 int64:
+ *  [0] agent_steps (sum over steps of live agents)  [1] steps
+ *  [2..5] per-species live count (last step)        [6..9] per-species health sum (last step)
+ *  [10] births (cumulative) [11] deaths [12] respawns [13] overflow (dropped spawns)
+ *  [14] food eaten [15] shots that hit
+ * These are the scalars a multi-GPU driver all-reduces (NCCL, sum). */
+int mbots_episode_stats(mbots_sim *sim, int64_t out[MBOTS_NUM_STATS], void *stream);
+
+/* Number of kernels this handle has launched since creation (bench bookkeeping). */
+int mbots_launch_count(mbots_sim *sim, uint64_t *out);
+
+/* Average device time in milliseconds of each of the step's kernels over the calls since
+ * the last reset (CUDA events on the launch stream; enabled by mbots_profile(sim, 1)).
+ * out[0] = step kernel, out[1] = row scan, out[2] = export+sensor kernel, out[3] = shift. */
+int mbots_profile(mbots_sim *sim, int32_t enable);
+int mbots_profile_read(mbots_sim *sim, float out_ms[4], uint32_t out_calls[4]);
+
+const char *mbots_last_error(void);
+const char *mbots_version(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* MBOTS_H */
