@@ -1,0 +1,466 @@
+/* mbots_api.cu -- the C-ABI of include/mbots.h over the kernels of sim_kernels.cu.
+ *
+ * Host-side counterpart of the reference's Manager (src/entry/mgr.cpp): owns the device
+ * memory of one simulator, launches the step, and hands out device pointers + dims for
+ * the exports. No CPU fallback: every entry point either drives the GPU or fails.
+ */
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <string.h>
+#include <string>
+#include <vector>
+#include <new>
+
+#include "../../include/mbots.h"
+#include "sim_dev.h"
+
+using namespace mbk;
+
+static thread_local std::string g_err;
+
+static int fail(int code, const char *what, cudaError_t ce = cudaSuccess)
+{
+    char buf[512];
+    if (ce != cudaSuccess) snprintf(buf, sizeof buf, "%s: %s", what, cudaGetErrorString(ce));
+    else snprintf(buf, sizeof buf, "%s", what);
+    g_err = buf;
+    return code;
+}
+
+#define CU(call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) return fail(MBOTS_ECUDA, #call, e_); } while (0)
+
+enum { K_STEP = 0, K_SCAN = 1, K_EXPORT = 2, K_SHIFT = 3, K_COUNT = 4 };
+
+struct mbots_sim {
+    mbots_config cfg;
+    SimDev d;
+    int cur;                       /* obs set that holds the current exports */
+    int device;
+    std::vector<void *> allocs;
+    Totals *hTotals;               /* pinned mirror of d.totals */
+    long long *dStats, *hStats;    /* 16 x int64 */
+    void *dbg;                     /* scratch for debug gathers: rows * 16 B */
+    uint32_t totalAgents;          /* host copy, valid after a sync */
+    bool dirty;                    /* async work enqueued since the last sync */
+    uint64_t launches;
+    /* per-kernel timing */
+    bool profile;
+    cudaEvent_t ev[5], evShift[2];
+    double ms[K_COUNT];
+    uint32_t calls[K_COUNT];
+};
+
+namespace {
+
+struct DeviceGuard {
+    int prev = -1;
+    bool ok = true;
+    explicit DeviceGuard(int dev)
+    {
+        if (cudaGetDevice(&prev) != cudaSuccess) { ok = false; return; }
+        if (prev != dev && cudaSetDevice(dev) != cudaSuccess) ok = false;
+    }
+    ~DeviceGuard() { if (prev >= 0) cudaSetDevice(prev); }
+};
+
+template <typename T>
+int dev_alloc(mbots_sim *s, T **out, size_t count)
+{
+    void *p = nullptr;
+    size_t bytes = count * sizeof(T);
+    if (bytes == 0) bytes = 16;
+    cudaError_t e = cudaMalloc(&p, bytes);
+    if (e != cudaSuccess) return fail(e == cudaErrorMemoryAllocation ? MBOTS_ENOMEM : MBOTS_ECUDA, "cudaMalloc", e);
+    e = cudaMemset(p, 0, bytes);
+    if (e != cudaSuccess) return fail(MBOTS_ECUDA, "cudaMemset", e);
+    s->allocs.push_back(p);
+    *out = static_cast<T *>(p);
+    return MBOTS_OK;
+}
+
+#define ALLOC(ptr, count) do { int rc_ = dev_alloc(s, &(ptr), (count)); if (rc_ != MBOTS_OK) return rc_; } while (0)
+
+int alloc_obs(mbots_sim *s, ObsSet &o, size_t rows)
+{
+    ALLOC(o.action, rows * 6); ALLOC(o.prev_action, rows * 6);
+    ALLOC(o.hidden, rows * 16); ALLOC(o.prev_hidden, rows * 16);
+    ALLOC(o.reward, rows); ALLOC(o.prev_reward, rows);
+    ALLOC(o.position, rows * 2); ALLOC(o.prev_position, rows * 2);
+    ALLOC(o.health, rows); ALLOC(o.prev_health, rows);
+    ALLOC(o.surrounding, rows * 2); ALLOC(o.prev_surrounding, rows * 2);
+    ALLOC(o.stats, rows * 4); ALLOC(o.prev_stats, rows * 4);
+    ALLOC(o.semantic, rows * 32); ALLOC(o.prev_semantic, rows * 32);
+    ALLOC(o.depth, rows * 32); ALLOC(o.prev_depth, rows * 32);
+    return MBOTS_OK;
+}
+
+int alloc_all(mbots_sim *s)
+{
+    SimDev &d = s->d;
+    const size_t W = d.numWorlds, rows = W * d.cap;
+    ALLOC(d.pose, rows); ALLOC(d.health, rows); ALLOC(d.species, rows); ALLOC(d.target, rows);
+    ALLOC(d.scratch, rows);
+    ALLOC(d.worldCount, W); ALLOC(d.worldOffset, W); ALLOC(d.rngKey, W); ALLOC(d.rngCount, W);
+    ALLOC(d.numFood, W); ALLOC(d.food, W * 48);
+    ALLOC(d.speciesLive, W); ALLOC(d.rowBase[0], W); ALLOC(d.rowBase[1], W);
+    ALLOC(d.speciesCount, W); ALLOC(d.speciesReward, W); ALLOC(d.speciesHealth, W); ALLOC(d.wstats, W);
+    ALLOC(d.sensorIndex, rows); ALLOC(d.done, rows); ALLOC(d.reset, W);
+    ALLOC(d.totals, 1);
+    int rc = alloc_obs(s, d.obs[0], rows);
+    if (rc != MBOTS_OK) return rc;
+    rc = alloc_obs(s, d.obs[1], rows);
+    if (rc != MBOTS_OK) return rc;
+    ALLOC(s->dStats, 16);
+    {
+        float4 *tmp = nullptr;
+        ALLOC(tmp, rows);
+        s->dbg = tmp;
+    }
+    return MBOTS_OK;
+}
+
+void free_all(mbots_sim *s)
+{
+    for (void *p : s->allocs) cudaFree(p);
+    s->allocs.clear();
+    if (s->hTotals) cudaFreeHost(s->hTotals);
+    if (s->hStats) cudaFreeHost(s->hStats);
+    for (auto &e : s->ev) if (e) cudaEventDestroy(e);
+    for (auto &e : s->evShift) if (e) cudaEventDestroy(e);
+}
+
+int finish(mbots_sim *s, cudaStream_t st)
+{
+    CU(cudaStreamSynchronize(st));
+    s->totalAgents = s->hTotals->totalAgents;
+    s->dirty = false;
+    return MBOTS_OK;
+}
+
+int enqueue_repack(mbots_sim *s, cudaStream_t st, int with_sensors, int count_step)
+{
+    launch_scan(s->d, s->cur, count_step, st);
+    if (s->profile && with_sensors) cudaEventRecord(s->ev[2], st);
+    launch_export(s->d, s->cur, with_sensors, st);
+    if (s->profile && with_sensors) cudaEventRecord(s->ev[3], st);
+    CU(cudaGetLastError());
+    CU(cudaMemcpyAsync(s->hTotals, s->d.totals, sizeof(Totals), cudaMemcpyDeviceToHost, st));
+    s->cur ^= 1;
+    s->launches += 2;
+    s->dirty = true;
+    return MBOTS_OK;
+}
+
+int enqueue_step(mbots_sim *s, cudaStream_t st)
+{
+    if (s->profile) cudaEventRecord(s->ev[0], st);
+    launch_step(s->d, s->cur, st);
+    if (s->profile) cudaEventRecord(s->ev[1], st);
+    s->launches += 1;
+    int rc = enqueue_repack(s, st, 1, 1);
+    if (rc != MBOTS_OK) return rc;
+    if (s->profile) {
+        CU(cudaEventSynchronize(s->ev[3]));
+        float a = 0, b = 0, c = 0;
+        cudaEventElapsedTime(&a, s->ev[0], s->ev[1]);
+        cudaEventElapsedTime(&b, s->ev[1], s->ev[2]);
+        cudaEventElapsedTime(&c, s->ev[2], s->ev[3]);
+        s->ms[K_STEP] += a; s->ms[K_SCAN] += b; s->ms[K_EXPORT] += c;
+        s->calls[K_STEP]++; s->calls[K_SCAN]++; s->calls[K_EXPORT]++;
+    }
+    return MBOTS_OK;
+}
+
+} // namespace
+
+extern "C" {
+
+int mbots_create_ex(const mbots_config *cfg, mbots_sim **out)
+{
+    if (!cfg || !out) return fail(MBOTS_EINVAL, "null argument");
+    *out = nullptr;
+    if (cfg->num_worlds == 0) return fail(MBOTS_EINVAL, "num_worlds must be > 0");
+    uint32_t cap = cfg->max_agents_per_world;
+    if (cap == 0) {
+        cap = 4u * cfg->init_num_agents_per_world;
+        if (cap < 128u) cap = 128u;
+    }
+    cap = (cap + 31u) & ~31u;
+    if (cap < cfg->init_num_agents_per_world || cap > 1024u)
+        return fail(MBOTS_EINVAL, "per-world capacity must hold the initial agents and be <= 1024");
+    if ((uint64_t)cfg->num_worlds * cap > 0x7fffffffull) return fail(MBOTS_EINVAL, "num_worlds * capacity exceeds int32 rows");
+    int ndev = 0;
+    cudaError_t e = cudaGetDeviceCount(&ndev);
+    if (e != cudaSuccess || ndev == 0) return fail(MBOTS_ECUDA, "no CUDA device (this library has no CPU path)", e);
+    if (cfg->gpu_id < 0 || cfg->gpu_id >= ndev) return fail(MBOTS_EINVAL, "gpu_id out of range");
+
+    mbots_sim *s = new (std::nothrow) mbots_sim();
+    if (!s) return fail(MBOTS_ENOMEM, "host allocation failed");
+    s->cfg = *cfg;
+    s->cfg.max_agents_per_world = cap;
+    s->device = cfg->gpu_id;
+    memset(&s->d, 0, sizeof(s->d));
+    s->d.numWorlds = cfg->num_worlds; s->d.cap = cap; s->d.initAgents = cfg->init_num_agents_per_world;
+    s->d.worldIdOffset = cfg->world_id_offset; s->d.seed = cfg->rand_seed;
+    DeviceGuard g(s->device);
+    int rc = g.ok ? MBOTS_OK : fail(MBOTS_ECUDA, "cudaSetDevice");
+    if (rc == MBOTS_OK) rc = alloc_all(s);
+    if (rc == MBOTS_OK) {
+        cudaError_t e1 = cudaMallocHost((void **)&s->hTotals, sizeof(Totals));
+        cudaError_t e2 = cudaMallocHost((void **)&s->hStats, 16 * sizeof(long long));
+        if (e1 != cudaSuccess || e2 != cudaSuccess) rc = fail(MBOTS_ENOMEM, "cudaMallocHost");
+        else memset(s->hTotals, 0, sizeof(Totals));
+    }
+    if (rc == MBOTS_OK) {
+        for (auto &ev : s->ev) if (cudaEventCreate(&ev) != cudaSuccess) rc = fail(MBOTS_ECUDA, "cudaEventCreate");
+        for (auto &ev : s->evShift) if (cudaEventCreate(&ev) != cudaSuccess) rc = fail(MBOTS_ECUDA, "cudaEventCreate");
+    }
+    if (rc == MBOTS_OK) {
+        size_t sm1 = step_smem_bytes(cap), sm2 = export_smem_bytes(cap);
+        (void)sm1; (void)sm2;   /* both far below the 48 KB default limit for cap <= 1024 */
+        /* Sim::Sim for every world, then the first row assignment (no sensor pass: the
+         * reference's tensors are only meaningful after the first step()). */
+        launch_init(s->d, 0);
+        s->cur = 0;
+        s->launches = 1;
+        rc = enqueue_repack(s, 0, 0, 0);
+        if (rc == MBOTS_OK) rc = finish(s, 0);
+    }
+    if (rc != MBOTS_OK) { free_all(s); delete s; return rc; }
+    *out = s;
+    return MBOTS_OK;
+}
+
+int mbots_create(int32_t gpu_id, uint32_t num_worlds, uint32_t rand_seed,
+                 uint32_t init_num_agents_per_world, mbots_sim **out)
+{
+    mbots_config c;
+    memset(&c, 0, sizeof c);
+    c.gpu_id = gpu_id; c.num_worlds = num_worlds; c.rand_seed = rand_seed;
+    c.init_num_agents_per_world = init_num_agents_per_world;
+    return mbots_create_ex(&c, out);
+}
+
+int mbots_destroy(mbots_sim *s)
+{
+    if (!s) return fail(MBOTS_EINVAL, "null handle");
+    DeviceGuard g(s->device);
+    cudaDeviceSynchronize();
+    free_all(s);
+    delete s;
+    return MBOTS_OK;
+}
+
+int mbots_step_async(mbots_sim *s, void *stream)
+{
+    if (!s) return fail(MBOTS_EINVAL, "null handle");
+    DeviceGuard g(s->device);
+    return enqueue_step(s, (cudaStream_t)stream);
+}
+
+int mbots_sync(mbots_sim *s, void *stream)
+{
+    if (!s) return fail(MBOTS_EINVAL, "null handle");
+    DeviceGuard g(s->device);
+    return finish(s, (cudaStream_t)stream);
+}
+
+int mbots_step(mbots_sim *s, void *stream)
+{
+    if (!s) return fail(MBOTS_EINVAL, "null handle");
+    DeviceGuard g(s->device);
+    int rc = enqueue_step(s, (cudaStream_t)stream);
+    if (rc != MBOTS_OK) return rc;
+    return finish(s, (cudaStream_t)stream);
+}
+
+int mbots_shift_observations_async(mbots_sim *s, void *stream)
+{
+    if (!s) return fail(MBOTS_EINVAL, "null handle");
+    DeviceGuard g(s->device);
+    cudaStream_t st = (cudaStream_t)stream;
+    if (s->profile) cudaEventRecord(s->evShift[0], st);
+    /* grid sized from the capacity bound when the host count is stale */
+    launch_shift(s->d, s->cur, s->dirty ? s->d.numWorlds * s->d.cap : s->totalAgents, st);
+    if (s->profile) {
+        cudaEventRecord(s->evShift[1], st);
+        CU(cudaEventSynchronize(s->evShift[1]));
+        float a = 0;
+        cudaEventElapsedTime(&a, s->evShift[0], s->evShift[1]);
+        s->ms[K_SHIFT] += a; s->calls[K_SHIFT]++;
+    }
+    CU(cudaGetLastError());
+    s->launches += 1;
+    return MBOTS_OK;
+}
+
+int mbots_shift_observations(mbots_sim *s, void *stream)
+{
+    int rc = mbots_shift_observations_async(s, stream);
+    if (rc != MBOTS_OK) return rc;
+    DeviceGuard g(s->device);
+    CU(cudaStreamSynchronize((cudaStream_t)stream));
+    return MBOTS_OK;
+}
+
+int mbots_num_agents(mbots_sim *s, uint32_t *out)
+{
+    if (!s || !out) return fail(MBOTS_EINVAL, "null argument");
+    *out = s->totalAgents;
+    return MBOTS_OK;
+}
+
+int mbots_tensor(mbots_sim *s, int32_t id, void **dev_ptr, int64_t dims[2], int32_t *dtype)
+{
+    if (!s || !dev_ptr || !dims || !dtype) return fail(MBOTS_EINVAL, "null argument");
+    const ObsSet &o = s->d.obs[s->cur];
+    const int64_t A = s->totalAgents, W = s->d.numWorlds;
+    auto set = [&](void *p, int64_t d0, int64_t d1, int32_t dt) {
+        *dev_ptr = p; dims[0] = d0; dims[1] = d1; *dtype = dt; return (int)MBOTS_OK;
+    };
+    auto gather = [&](int what, int64_t cols, int32_t dt) {
+        DeviceGuard g(s->device);
+        launch_debug_gather(s->d, what, s->dbg, 0);
+        s->launches += 1;
+        cudaError_t e = cudaStreamSynchronize(0);
+        if (e != cudaSuccess) return fail(MBOTS_ECUDA, "debug gather", e);
+        return set(s->dbg, A, cols, dt);
+    };
+    switch (id) {
+    case MBOTS_EXPORT_RESET: return set(s->d.reset, W, 1, MBOTS_I32);
+    case MBOTS_EXPORT_ACTION: return set(o.action, A, 6, MBOTS_I32);
+    case MBOTS_EXPORT_PREV_ACTION: return set(o.prev_action, A, 6, MBOTS_I32);
+    case MBOTS_EXPORT_HIDDEN_STATE: return set(o.hidden, A, 16, MBOTS_F32);
+    case MBOTS_EXPORT_PREV_HIDDEN_STATE: return set(o.prev_hidden, A, 16, MBOTS_F32);
+    case MBOTS_EXPORT_REWARD: return set(o.reward, A, 1, MBOTS_F32);
+    case MBOTS_EXPORT_PREV_REWARD: return set(o.prev_reward, A, 1, MBOTS_F32);
+    case MBOTS_EXPORT_DONE: return set(s->d.done, A, 1, MBOTS_I32);
+    case MBOTS_EXPORT_POSITION: return set(o.position, A, 2, MBOTS_F32);
+    case MBOTS_EXPORT_PREV_POSITION: return set(o.prev_position, A, 2, MBOTS_F32);
+    case MBOTS_EXPORT_HEALTH: return set(o.health, A, 1, MBOTS_F32);
+    case MBOTS_EXPORT_PREV_HEALTH: return set(o.prev_health, A, 1, MBOTS_F32);
+    case MBOTS_EXPORT_SURROUNDING: return set(o.surrounding, A, 2, MBOTS_F32);
+    case MBOTS_EXPORT_PREV_SURROUNDING: return set(o.prev_surrounding, A, 2, MBOTS_F32);
+    case MBOTS_EXPORT_SENSOR_SEMANTIC: return set(o.semantic, A, 32, MBOTS_I8);
+    case MBOTS_EXPORT_SENSOR_DEPTH: return set(o.depth, A, 32, MBOTS_U8);
+    case MBOTS_EXPORT_PREV_SENSOR_SEMANTIC: return set(o.prev_semantic, A, 32, MBOTS_I8);
+    case MBOTS_EXPORT_PREV_SENSOR_DEPTH: return set(o.prev_depth, A, 32, MBOTS_U8);
+    case MBOTS_EXPORT_STATS: return set(o.stats, A, 4, MBOTS_I32);
+    case MBOTS_EXPORT_PREV_STATS: return set(o.prev_stats, A, 4, MBOTS_I32);
+    case MBOTS_EXPORT_SENSOR_INDEX: return set(s->d.sensorIndex, A, 1, MBOTS_I32);
+    case MBOTS_EXPORT_SPECIES_COUNT: return set(s->d.speciesCount, W, 4, MBOTS_I32);
+    case MBOTS_DEBUG_WORLD_COUNT: return set(s->d.worldCount, W, 1, MBOTS_I32);
+    case MBOTS_DEBUG_WORLD_OFFSET: return set(s->d.worldOffset, W, 1, MBOTS_I32);
+    case MBOTS_DEBUG_RNG_COUNT: return set(s->d.rngCount, W, 1, MBOTS_I32);
+    case MBOTS_DEBUG_NUM_FOOD: return set(s->d.numFood, W, 1, MBOTS_I32);
+    case MBOTS_DEBUG_FOOD: return set(s->d.food, W * 48, 8, MBOTS_U8);
+    case MBOTS_DEBUG_ROW_BASE: return set(s->d.rowBase[s->cur], W, 4, MBOTS_I32);
+    case MBOTS_DEBUG_POSE: return gather(0, 4, MBOTS_F32);
+    case MBOTS_DEBUG_AGENT_HEALTH: return gather(1, 1, MBOTS_I32);
+    case MBOTS_DEBUG_AGENT_SPECIES: return gather(2, 1, MBOTS_I32);
+    case MBOTS_DEBUG_AGENT_TARGET: return gather(3, 1, MBOTS_I32);
+    default: return fail(MBOTS_EINVAL, "unknown export id");
+    }
+}
+
+int mbots_set_action(mbots_sim *s, uint32_t agent_idx, int32_t forward, int32_t backward,
+                     int32_t rotate_left, int32_t rotate_right, int32_t shoot, int32_t breed)
+{
+    if (!s) return fail(MBOTS_EINVAL, "null handle");
+    if (agent_idx >= s->totalAgents) return fail(MBOTS_EINVAL, "agent index out of range");
+    DeviceGuard g(s->device);
+    const int32_t a[6] = {forward, backward, rotate_left, rotate_right, shoot, breed};
+    CU(cudaMemcpy(s->d.obs[s->cur].action + (size_t)agent_idx * 6, a, sizeof a, cudaMemcpyHostToDevice));
+    return MBOTS_OK;
+}
+
+int mbots_agent_offset_for_world(mbots_sim *s, uint32_t world_idx, uint32_t *out)
+{
+    if (!s || !out) return fail(MBOTS_EINVAL, "null argument");
+    if (world_idx >= s->d.numWorlds) return fail(MBOTS_EINVAL, "world index out of range");
+    DeviceGuard g(s->device);
+    int32_t v = 0;
+    CU(cudaMemcpy(&v, s->d.worldOffset + world_idx, sizeof v, cudaMemcpyDeviceToHost));
+    *out = (uint32_t)v;
+    return MBOTS_OK;
+}
+
+static int export_bytes(mbots_sim *s, int32_t id, void **p, uint64_t *bytes)
+{
+    int64_t dims[2];
+    int32_t dt;
+    int rc = mbots_tensor(s, id, p, dims, &dt);
+    if (rc != MBOTS_OK) return rc;
+    const uint64_t es = (dt == MBOTS_I32 || dt == MBOTS_F32) ? 4u : 1u;
+    *bytes = (uint64_t)dims[0] * (uint64_t)dims[1] * es;
+    return MBOTS_OK;
+}
+
+int mbots_copy_from_host(mbots_sim *s, int32_t id, const void *host, uint64_t bytes, void *stream)
+{
+    if (!s || !host) return fail(MBOTS_EINVAL, "null argument");
+    void *p; uint64_t have;
+    int rc = export_bytes(s, id, &p, &have);
+    if (rc != MBOTS_OK) return rc;
+    if (bytes > have) return fail(MBOTS_EINVAL, "copy larger than the export");
+    DeviceGuard g(s->device);
+    CU(cudaMemcpyAsync(p, host, bytes, cudaMemcpyHostToDevice, (cudaStream_t)stream));
+    return MBOTS_OK;
+}
+
+int mbots_copy_to_host(mbots_sim *s, int32_t id, void *host, uint64_t bytes, void *stream)
+{
+    if (!s || !host) return fail(MBOTS_EINVAL, "null argument");
+    void *p; uint64_t have;
+    int rc = export_bytes(s, id, &p, &have);
+    if (rc != MBOTS_OK) return rc;
+    if (bytes > have) return fail(MBOTS_EINVAL, "copy larger than the export");
+    DeviceGuard g(s->device);
+    CU(cudaMemcpyAsync(host, p, bytes, cudaMemcpyDeviceToHost, (cudaStream_t)stream));
+    return MBOTS_OK;
+}
+
+int mbots_episode_stats(mbots_sim *s, int64_t out[MBOTS_NUM_STATS], void *stream)
+{
+    if (!s || !out) return fail(MBOTS_EINVAL, "null argument");
+    DeviceGuard g(s->device);
+    cudaStream_t st = (cudaStream_t)stream;
+    launch_stats_reduce(s->d, s->dStats, st);
+    s->launches += 1;
+    CU(cudaGetLastError());
+    CU(cudaMemcpyAsync(s->hStats, s->dStats, 16 * sizeof(long long), cudaMemcpyDeviceToHost, st));
+    CU(cudaStreamSynchronize(st));
+    for (int i = 0; i < MBOTS_NUM_STATS; ++i) out[i] = (int64_t)s->hStats[i];
+    return MBOTS_OK;
+}
+
+int mbots_launch_count(mbots_sim *s, uint64_t *out)
+{
+    if (!s || !out) return fail(MBOTS_EINVAL, "null argument");
+    *out = s->launches;
+    return MBOTS_OK;
+}
+
+int mbots_profile(mbots_sim *s, int32_t enable)
+{
+    if (!s) return fail(MBOTS_EINVAL, "null handle");
+    s->profile = enable != 0;
+    for (int i = 0; i < K_COUNT; ++i) { s->ms[i] = 0; s->calls[i] = 0; }
+    return MBOTS_OK;
+}
+
+int mbots_profile_read(mbots_sim *s, float out_ms[4], uint32_t out_calls[4])
+{
+    if (!s || !out_ms || !out_calls) return fail(MBOTS_EINVAL, "null argument");
+    for (int i = 0; i < K_COUNT; ++i) {
+        out_calls[i] = s->calls[i];
+        out_ms[i] = s->calls[i] ? (float)(s->ms[i] / s->calls[i]) : 0.f;
+    }
+    return MBOTS_OK;
+}
+
+const char *mbots_last_error(void) { return g_err.c_str(); }
+const char *mbots_version(void) { return "mbots-b200 0.1 (sm_100a)"; }
+
+} /* extern "C" */

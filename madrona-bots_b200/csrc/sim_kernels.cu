@@ -1,0 +1,741 @@
+/* sim_kernels.cu -- the per-step hot path of madrona-bots as four sm_100a kernels.
+ *
+ *   step_kernel    one CTA per world, one thread per agent slot. Restates the Step task
+ *                  graph up to the world sort (src/sim/sim.cpp:1061-1132): chunk reset,
+ *                  food spawn, actionSystem, healthSync, surroundings, species tracker,
+ *                  speciesInfoSync + respawn, and the compaction the reference gets from
+ *                  SortArchetypeNode<Agent, WorldID>. World state lives in shared memory
+ *                  for the duration; every cross-agent effect (shots, chunk counters,
+ *                  food, births) is a shared-memory atomic or a block scan.
+ *   scan_kernel    the only cross-world dependency: exclusive scan of the per-(world,
+ *                  species) row counts in species-major order -> first row of each
+ *                  (world, species) segment. Replaces the global radix sort by
+ *                  SpeciesObservation (src/sim/sim.cpp:1148-1149).
+ *   export_kernel  one CTA per world. Gathers every column that travels with an agent from
+ *                  its old row to its new row (the "sort"), writes the observation exports
+ *                  (updateObservations :687-717, updateSensorOutputIdx :736-789, rewardSystem
+ *                  :840-983) and runs the 32-ray sensor over the world's agents staged in
+ *                  shared memory (M/src/mw/device/bvh_raycast.cpp:193-305; exhaustive nearest
+ *                  hit instead of a TLAS).
+ *   shift_kernel   shiftObservationsSystem + shiftHiddenState (src/sim/sim.cpp:1002-1048).
+ *
+ * Compiled with -fmad=false: results must be bit-identical to the CPU oracle.
+ */
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include "sim_dev.h"
+#include "sim_prims.cuh"
+
+namespace mbk {
+using namespace mbp;
+
+#define FULL 0xffffffffu
+
+/* ------------------------------------------------------------------------- */
+/* small block-level helpers                                                   */
+
+/* Exclusive scan of a 0/1 flag over the CTA in thread order. `wc` is a shared int[32].
+ * Contains two barriers; must be called by every thread of the CTA. */
+__device__ __forceinline__ int block_scan_flag(bool flag, int &total, int *wc)
+{
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nw = (blockDim.x + 31) >> 5;
+    const unsigned b = __ballot_sync(FULL, flag);
+    const int in_warp = __popc(b & ((1u << lane) - 1u));
+    if (lane == 0) wc[warp] = __popc(b);
+    __syncthreads();
+    int base = 0, tot = 0;
+    for (int i = 0; i < nw; ++i) { const int c = wc[i]; if (i < warp) base += c; tot += c; }
+    __syncthreads();
+    total = tot;
+    return base + in_warp;
+}
+
+/* Rank of this thread among lower threads of the same species (sp in 0..3, or -1 for
+ * "not an agent"), and the per-species totals. `wc` is a shared uint32[32] (8 bits per
+ * species per warp). Two barriers. */
+__device__ __forceinline__ int block_species_rank(int sp, int tot[4], uint32_t *wc)
+{
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nw = (blockDim.x + 31) >> 5;
+    const unsigned lt = (1u << lane) - 1u;
+    uint32_t packed = 0;
+    int in_warp = 0;
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+        const unsigned b = __ballot_sync(FULL, sp == k);
+        packed |= (uint32_t)__popc(b) << (8 * k);   /* <= 32 per warp: fits 8 bits */
+        if (sp == k) in_warp = __popc(b & lt);
+    }
+    if (lane == 0) wc[warp] = packed;
+    __syncthreads();
+    int base = 0;
+    tot[0] = tot[1] = tot[2] = tot[3] = 0;
+    for (int i = 0; i < nw; ++i) {
+        const uint32_t p = wc[i];
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            const int c = (int)((p >> (8 * k)) & 0xffu);
+            tot[k] += c;
+            if (i < warp && sp == k) base += c;
+        }
+    }
+    __syncthreads();
+    return base + in_warp;
+}
+
+__device__ __forceinline__ int comp(const int4 &v, int k)
+{
+    return k == 0 ? v.x : k == 1 ? v.y : k == 2 ? v.z : v.w;
+}
+
+/* ------------------------------------------------------------------------- */
+/* init: Sim::Sim + initWorld + initializeChunks (src/sim/sim.cpp:1232-1256, 233-300) */
+
+__global__ void init_kernel(SimDev d)
+{
+    const uint32_t w = blockIdx.x;
+    const uint32_t s = threadIdx.x;
+    const Key key = key_split(key_init(d.seed), 0u, d.worldIdOffset + w);
+    const size_t base = (size_t)w * d.cap;
+    if (s < d.initAgents) {
+        const float x = key_sample_uniform(key_split(key, 2u * s)) * kWorldX;
+        const float y = key_sample_uniform(key_split(key, 2u * s + 1u)) * kWorldY;
+        d.pose[base + s] = make_float4(x, y, 1.f, 0.f);
+        d.health[base + s] = 100;
+        d.species[base + s] = (uint8_t)((s % kNumSpecies) + 1u);
+        d.target[base + s] = (int16_t)-1;
+        d.scratch[base + s] = make_float4(__int_as_float(-1), 0.f, 0.f, __int_as_float(0));
+    }
+    if (s < (uint32_t)kNumChunks) d.food[(size_t)w * kNumChunks + s] = make_uint2(0u, 0u);
+    if (s == 0) {
+        d.worldCount[w] = (int32_t)d.initAgents;
+        d.rngKey[w] = make_uint2(key.a, key.b);
+        d.rngCount[w] = 2u * d.initAgents;
+        d.numFood[w] = 0;
+        int4 c;
+        const int q = (int)(d.initAgents / kNumSpecies), r = (int)(d.initAgents % kNumSpecies);
+        c.x = q + (r > 0); c.y = q + (r > 1); c.z = q + (r > 2); c.w = q;
+        d.speciesLive[w] = c;
+        d.speciesCount[w] = make_int4(0, 0, 0, 0);
+        d.speciesReward[w] = make_float4(0.f, 0.f, 0.f, 0.f);
+        d.speciesHealth[w] = make_int4(0, 0, 0, 0);
+        WorldStats z = {0, 0, 0, 0, 0, 0, 0, 0};
+        d.wstats[w] = z;
+    }
+}
+
+/* ------------------------------------------------------------------------- */
+/* step_kernel                                                                 */
+
+struct StepShared {
+    uint32_t chunkAgents[kNumChunks];
+    uint32_t chunkSpeed[kNumChunks];
+    uint2 food[kNumChunks];
+    Key draws[32];
+    int wc[32];
+    uint32_t wcs[32];
+    uint32_t cnt[4], hsum[4];
+    uint32_t rngCount;
+    int32_t numFood;
+    uint32_t foodDirty, eaten, shots;
+    /* followed by: int accum[cap]; uint32 wantKey[cap]; uint32 wantMask[cap/32]; uint32 ateMask[cap/32]; uint8 species[cap] */
+};
+
+size_t step_smem_bytes(uint32_t cap)
+{
+    return sizeof(StepShared) + (size_t)cap * (4 + 4 + 1) + (size_t)(cap / 32) * 8 + 16;
+}
+
+/* addFoodSystem + addFoodToChunk (src/sim/sim.cpp:308-387) for one world, executed by
+ * one thread from 32 pre-split draw keys (the stream is counter-based, so draw k is
+ * split_i(key, count + k) whatever happened before it). At most 2 + 3*7 = 23 draws. */
+__device__ __forceinline__ void add_food(StepShared &sh)
+{
+    uint32_t k = 0;
+    if (key_sample_i32(sh.draws[k++], 0, 10) == 0) {
+        uint32_t n = (uint32_t)key_sample_i32(sh.draws[k++], 1, 3);
+        const uint32_t allowed = (uint32_t)kTotalAllowedFood - (uint32_t)sh.numFood;   /* unsigned, U12 */
+        n = n < allowed ? n : allowed;
+        for (uint32_t i = 0; i < n; ++i) {
+            const uint32_t cx = (uint32_t)key_sample_i32(sh.draws[k++], 0, kChunksX);
+            const uint32_t cy = (uint32_t)key_sample_i32(sh.draws[k++], 0, kChunksY);
+            k += 2;                                     /* two discarded draws (:311-312) */
+            uint2 f = sh.food[cx + cy * kChunksX];
+            const uint32_t mask = (f.y >> 8) & 0x1fu;
+            if (mask != 0x1fu) {
+                const uint32_t p = (uint32_t)__ffs((int)(~mask & 0x1fu)) - 1u;   /* first empty package */
+                const uint32_t rx = (uint32_t)key_sample_i32(sh.draws[k++], 0, kChunkWidth);
+                const uint32_t ry = (uint32_t)key_sample_i32(sh.draws[k++], 0, kChunkWidth);
+                k += 1;                                 /* yaw of the render-only food entity (:340) */
+                const uint32_t cell = (rx << 4) | ry;
+                if (p < 4u) f.x = (f.x & ~(0xffu << (8 * p))) | (cell << (8 * p));
+                else f.y = (f.y & ~0xffu) | cell;
+                f.y |= 1u << (8 + p);
+                sh.food[cx + cy * kChunksX] = f;
+                sh.numFood += 1;
+                sh.foodDirty = 1;
+            }
+        }
+    }
+    sh.rngCount += k;
+}
+
+__device__ __forceinline__ uint32_t food_cell(const uint2 &f, int p)
+{
+    return p < 4 ? (f.x >> (8 * p)) & 0xffu : f.y & 0xffu;
+}
+
+/* packages of chunk record `f` that hold food at `cell` */
+__device__ __forceinline__ uint32_t food_match(const uint2 &f, uint32_t cell)
+{
+    const uint32_t has = (f.y >> 8) & 0x1fu;
+    uint32_t m = 0;
+#pragma unroll
+    for (int p = 0; p < kMaxFoodPackages; ++p)
+        if (food_cell(f, p) == cell) m |= 1u << p;
+    return m & has;
+}
+
+__global__ void step_kernel(SimDev d, int cur)
+{
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    StepShared &sh = *reinterpret_cast<StepShared *>(smem_raw);
+    const uint32_t cap = d.cap;
+    int *accum = reinterpret_cast<int *>(smem_raw + sizeof(StepShared));
+    uint32_t *wantKey = reinterpret_cast<uint32_t *>(accum + cap);
+    uint32_t *wantMask = wantKey + cap;
+    uint32_t *ateMask = wantMask + cap / 32;
+    uint8_t *spec = reinterpret_cast<uint8_t *>(ateMask + cap / 32);
+
+    const uint32_t w = blockIdx.x;
+    const uint32_t s = threadIdx.x;
+    const size_t base = (size_t)w * cap;
+    const ObsSet &from = d.obs[cur];
+
+    /* ---- P0: stage the world ---- */
+    const int n0 = d.worldCount[w];
+    const bool active = (int)s < n0;
+    float4 pose = make_float4(0.f, 0.f, 1.f, 0.f);
+    int hp = 0, sp = 0, tgt = -1;
+    if (active) {
+        pose = d.pose[base + s];
+        hp = d.health[base + s];
+        sp = d.species[base + s];
+        tgt = d.target[base + s];
+    }
+    accum[s] = hp;
+    spec[s] = (uint8_t)sp;
+    if (s < cap / 32) { wantMask[s] = 0; ateMask[s] = 0; }
+    for (uint32_t c = s; c < (uint32_t)kNumChunks; c += blockDim.x) {
+        sh.chunkAgents[c] = 0;                         /* resetChunkInfoSystem (:390-396) */
+        sh.chunkSpeed[c] = 0;
+        sh.food[c] = d.food[(size_t)w * kNumChunks + c];
+    }
+    uint32_t rng0 = 0;
+    if (s < 32) {
+        const uint2 kk = d.rngKey[w];
+        rng0 = d.rngCount[w];
+        sh.draws[s] = key_split(Key{kk.x, kk.y}, rng0 + s);
+        if (s < 4) { sh.cnt[s] = 0; sh.hsum[s] = 0; }
+        if (s == 0) {
+            sh.rngCount = rng0;
+            sh.numFood = d.numFood[w];
+            sh.foodDirty = 0; sh.eaten = 0; sh.shots = 0;
+        }
+    }
+    /* the agent's observation row in set `cur` (rank among lower slots of its species) */
+    int tot0[4];
+    const int rank0 = block_species_rank(active ? sp - 1 : -1, tot0, sh.wcs);   /* barriers */
+    int act[6] = {0, 0, 0, 0, 0, 0};
+    int oldrow = -1;
+    if (active) {
+        oldrow = comp(d.rowBase[cur][w], sp - 1) + rank0;
+        const int2 *ap = reinterpret_cast<const int2 *>(from.action + (size_t)oldrow * 6);
+        const int2 a0 = ap[0], a1 = ap[1], a2 = ap[2];
+        act[0] = a0.x; act[1] = a0.y; act[2] = a1.x; act[3] = a1.y; act[4] = a2.x; act[5] = a2.y;
+    }
+
+    /* ---- P1: addFoodSystem (thread 0) and actionSystem (every agent) ---- */
+    if (s == 0) add_food(sh);
+    uint32_t stat = 0;   /* bit0 hitFriendly, bit1 hitEnemy, bit2 ateFood, bit3 reproduced */
+    if (active) {
+        if (act[4] && tgt >= 0) {                      /* shoot with last frame's finder hit (:434-454) */
+            atomicAdd(&accum[tgt], -50);
+            atomicAdd(&sh.shots, 1u);
+            stat |= (spec[tgt] == sp) ? 1u : 2u;
+        }
+        Rot rot{pose.z, pose.w};
+        const float len = move_agent(pose.x, pose.y, rot, act[0] != 0, act[1] != 0, act[2] != 0, act[3] != 0);
+        pose.z = rot.w; pose.w = rot.z;
+        const int c = chunk_of(pose.x, pose.y);
+        atomicAdd(&sh.chunkAgents[c], 1u);
+        atomicAdd(&sh.chunkSpeed[c], (uint32_t)(len * 2.f));
+    }
+    __syncthreads();
+
+    /* ---- P2: healthSync (:505-581) ---- */
+    hp = accum[s];
+    const int mychunk = active ? chunk_of(pose.x, pose.y) : 0;
+    const uint32_t mycell = cell_of(pose.x, pose.y);
+    const bool wants = active && food_match(sh.food[mychunk], mycell) != 0;
+    if (__syncthreads_or(wants)) {
+        /* Rare: at least one agent stands on food. Resolve in slot order so that the lowest
+         * slot wins a contested package (FoodPackage::consume CAS race, sim.inl:76-99; U11). */
+        if (wants) {
+            wantKey[s] = ((uint32_t)mychunk << 8) | mycell;
+            atomicOr(&wantMask[s >> 5], 1u << (s & 31));
+        }
+        __syncthreads();
+        if (s == 0) {
+            for (uint32_t wd = 0; wd < cap / 32; ++wd) {
+                uint32_t m = wantMask[wd];
+                while (m) {
+                    const uint32_t b = (uint32_t)__ffs((int)m) - 1u;
+                    m &= m - 1u;
+                    const uint32_t slot = wd * 32 + b, key = wantKey[slot];
+                    uint2 f = sh.food[key >> 8];
+                    const uint32_t mm = food_match(f, key & 0xffu);
+                    if (mm) {
+                        const uint32_t p = (uint32_t)__ffs((int)mm) - 1u;
+                        f.y &= ~(1u << (8 + p));
+                        sh.food[key >> 8] = f;
+                        sh.numFood -= 1;
+                        sh.eaten += 1;
+                        sh.foodDirty = 1;
+                        ateMask[wd] |= 1u << b;
+                    }
+                }
+            }
+        }
+        __syncthreads();
+        if (active && (ateMask[s >> 5] >> (s & 31) & 1u)) { hp += 20; stat |= 4u; }
+    }
+    bool breeds = false;
+    if (active && act[5] && hp > 10 && tgt >= 0 && spec[tgt] == sp) {
+        hp -= 40;
+        stat |= 8u;
+        breeds = true;
+    }
+    const bool live = active && hp > 0;
+    int nBreed, nLive;
+    const int bidx = block_scan_flag(breeds, nBreed, sh.wc);
+    const int lidx = block_scan_flag(live, nLive, sh.wc);
+    const int room = (int)cap - n0;                    /* makeAgent fails once the slot table is full (D1) */
+    const int bornOk = nBreed < room ? nBreed : room;
+    const bool childOk = breeds && bidx < room;
+
+    /* updateSurroundingObservation (:583-654); a newborn shares its parent's position */
+    float sn = 0.f, ss = 0.f;
+    if (live || childOk) surroundings(pose.x, pose.y, sh.chunkAgents, sh.chunkSpeed, sn, ss);
+
+    /* speciesTrackerUpdate (:719-734) */
+    if (live) { atomicAdd(&sh.cnt[sp - 1], 1u); atomicAdd(&sh.hsum[sp - 1], (uint32_t)hp); }
+    if (childOk) { atomicAdd(&sh.cnt[sp - 1], 1u); atomicAdd(&sh.hsum[sp - 1], 50u); }
+
+    /* compaction: survivors keep their order, then newborns in parent order (U11) */
+    if (live) {
+        const size_t o = base + (size_t)lidx;
+        d.pose[o] = pose;
+        d.health[o] = hp;
+        d.species[o] = (uint8_t)sp;
+        d.scratch[o] = make_float4(__int_as_float(oldrow), sn, ss, __int_as_float((int)stat));
+    }
+    if (childOk) {
+        const size_t o = base + (size_t)(nLive + bidx);
+        d.pose[o] = make_float4(pose.x, pose.y, 1.f, 0.f);
+        d.health[o] = 50;
+        d.species[o] = (uint8_t)sp;
+        d.scratch[o] = make_float4(__int_as_float(-1), sn, ss, __int_as_float(0));
+    }
+    __syncthreads();
+
+    /* ---- P3: speciesInfoSync + respawn (:791-838) ---- */
+    const uint32_t q = d.initAgents / kNumSpecies;
+    uint32_t c4[4], need[4], pre[4];
+    uint32_t needTotal = 0;
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+        c4[k] = sh.cnt[k];
+        need[k] = c4[k] < q ? q - c4[k] : 0u;
+        pre[k] = needTotal;
+        needTotal += need[k];
+    }
+    const int size1 = n0 + bornOk;                     /* table size before respawn (dead rows still count) */
+    const int room2 = (int)cap - size1;
+    const uint32_t respOk = (int)needTotal < room2 ? needTotal : (uint32_t)room2;
+    const uint32_t rngBase = sh.rngCount;
+    if (s < needTotal) {
+        int k = 0;
+        if (s >= pre[1] + need[1]) k = (s >= pre[2] + need[2]) ? 3 : 2;
+        else if (s >= pre[0] + need[0]) k = 1;
+        const uint2 kk = d.rngKey[w];
+        const Key key{kk.x, kk.y};
+        const float x = key_sample_uniform(key_split(key, rngBase + 2u * s)) * kWorldX;
+        const float y = key_sample_uniform(key_split(key, rngBase + 2u * s + 1u)) * kWorldY;
+        if (s < respOk) {
+            const size_t o = base + (size_t)(nLive + bornOk) + s;
+            d.pose[o] = make_float4(x, y, 1.f, 0.f);
+            d.health[o] = 100;
+            d.species[o] = (uint8_t)(k + 1);
+            d.scratch[o] = make_float4(__int_as_float(-1), 0.f, 0.f, __int_as_float(0));
+        }
+    }
+    if (s == 0) {
+        int4 liveRows;
+        int *lr = &liveRows.x;
+        float4 rw;
+        float *rwp = &rw.x;
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            const uint32_t ok = respOk > pre[k] ? (respOk - pre[k] < need[k] ? respOk - pre[k] : need[k]) : 0u;
+            lr[k] = (int)(c4[k] + ok);
+            rwp[k] = species_reward(c4[k], sh.hsum[k], d.initAgents);
+        }
+        d.speciesLive[w] = liveRows;
+        d.speciesCount[w] = make_int4((int)c4[0], (int)c4[1], (int)c4[2], (int)c4[3]);
+        d.speciesHealth[w] = make_int4((int)sh.hsum[0], (int)sh.hsum[1], (int)sh.hsum[2], (int)sh.hsum[3]);
+        d.speciesReward[w] = rw;
+        d.worldCount[w] = nLive + bornOk + (int)respOk;
+        d.rngCount[w] = rngBase + 2u * needTotal;
+        d.numFood[w] = sh.numFood;
+        const uint32_t deaths = (uint32_t)(n0 - nLive);
+        const uint32_t overflow = (uint32_t)(nBreed - bornOk) + (needTotal - respOk);
+        if (bornOk | (int)deaths | (int)respOk | (int)overflow | (int)sh.eaten | (int)sh.shots) {
+            WorldStats ws = d.wstats[w];
+            ws.births += (uint32_t)bornOk; ws.deaths += deaths; ws.respawns += respOk;
+            ws.overflow += overflow; ws.eaten += sh.eaten; ws.shots += sh.shots;
+            d.wstats[w] = ws;
+        }
+    }
+    if (sh.foodDirty)
+        for (uint32_t c = s; c < (uint32_t)kNumChunks; c += blockDim.x) d.food[(size_t)w * kNumChunks + c] = sh.food[c];
+}
+
+/* ------------------------------------------------------------------------- */
+/* scan_kernel: rows are ordered (species, world, slot). One CTA. */
+
+constexpr int kScanThreads = 1024;
+
+__device__ __forceinline__ int warp_incl_scan(int v)
+{
+    const int lane = threadIdx.x & 31;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const int t = __shfl_up_sync(FULL, v, o);
+        if (lane >= o) v += t;
+    }
+    return v;
+}
+
+__global__ void __launch_bounds__(kScanThreads) scan_kernel(SimDev d, int cur, int count_step)
+{
+    __shared__ int red[32][4];
+    __shared__ int wsum[32][5];
+    __shared__ int carry[5];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int W = (int)d.numWorlds;
+
+    /* pass 1: rows per species */
+    int t4[4] = {0, 0, 0, 0};
+    for (int w = tid; w < W; w += kScanThreads) {
+        const int4 c = d.speciesLive[w];
+        t4[0] += c.x; t4[1] += c.y; t4[2] += c.z; t4[3] += c.w;
+    }
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+        int v = t4[k];
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(FULL, v, o);
+        if (lane == 0) red[warp][k] = v;
+    }
+    __syncthreads();
+    if (tid == 0) {
+        int tot[4] = {0, 0, 0, 0};
+        for (int i = 0; i < kScanThreads / 32; ++i)
+            for (int k = 0; k < 4; ++k) tot[k] += red[i][k];
+        int b = 0;
+        for (int k = 0; k < 4; ++k) { carry[k] = b; b += tot[k]; d.totals->speciesTotal[k] = (uint32_t)tot[k]; }
+        carry[4] = 0;
+        d.totals->totalAgents = (uint32_t)b;
+        if (count_step) { d.totals->agentSteps += (unsigned long long)b; d.totals->steps += 1ull; }
+    }
+    __syncthreads();
+
+    /* pass 2: tile-wise exclusive scan with a running carry */
+    int4 *rb = d.rowBase[cur ^ 1];
+    for (int w0 = 0; w0 < W; w0 += kScanThreads) {
+        const int w = w0 + tid;
+        int4 c = make_int4(0, 0, 0, 0);
+        if (w < W) c = d.speciesLive[w];
+        int v[5] = {c.x, c.y, c.z, c.w, c.x + c.y + c.z + c.w};
+        int inc[5];
+#pragma unroll
+        for (int k = 0; k < 5; ++k) {
+            inc[k] = warp_incl_scan(v[k]);
+            if (lane == 31) wsum[warp][k] = inc[k];
+        }
+        __syncthreads();
+        int basek[5];
+#pragma unroll
+        for (int k = 0; k < 5; ++k) {
+            int b = carry[k];
+            for (int i = 0; i < warp; ++i) b += wsum[i][k];
+            basek[k] = b;
+        }
+        if (w < W) {
+            rb[w] = make_int4(basek[0] + inc[0] - v[0], basek[1] + inc[1] - v[1],
+                              basek[2] + inc[2] - v[2], basek[3] + inc[3] - v[3]);
+            d.worldOffset[w] = basek[4] + inc[4] - v[4];
+        }
+        __syncthreads();
+        if (tid == kScanThreads - 1) {
+#pragma unroll
+            for (int k = 0; k < 5; ++k) carry[k] = basek[k] + inc[k];
+        }
+        __syncthreads();
+    }
+}
+
+/* ------------------------------------------------------------------------- */
+/* export_kernel                                                               */
+
+constexpr int kExportThreads = 128;
+
+struct ExportAgent { float x, y; int newrow, oldrow; };
+
+size_t export_smem_bytes(uint32_t cap)
+{
+    return (size_t)cap * (sizeof(ExportAgent) + 4 /*theta*/ + 1 /*species*/) + 16;
+}
+
+/* Copy one column of every agent of the world from its old row to its new row.
+ * VEC = bytes per lane access, PARTS = row bytes / VEC. A created-this-step record
+ * (old row < 0) is zero-filled (DEVIATIONS.md D3). */
+template <typename V, int PARTS>
+__device__ __forceinline__ void carry_column(void *dst, const void *src, const ExportAgent *ag, int n)
+{
+    const int tasks = n * PARTS;
+    V *dp = reinterpret_cast<V *>(dst);
+    const V *sp = reinterpret_cast<const V *>(src);
+    for (int t = threadIdx.x; t < tasks; t += kExportThreads) {
+        const int a = t / PARTS, p = t - a * PARTS;
+        const int o = ag[a].oldrow;
+        V v = V();
+        if (o >= 0) v = sp[(size_t)o * PARTS + p];
+        dp[(size_t)ag[a].newrow * PARTS + p] = v;
+    }
+}
+
+__global__ void __launch_bounds__(kExportThreads) export_kernel(SimDev d, int cur, int with_sensors)
+{
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    const uint32_t cap = d.cap;
+    ExportAgent *ag = reinterpret_cast<ExportAgent *>(smem_raw);
+    float *theta = reinterpret_cast<float *>(ag + cap);
+    uint8_t *spec = reinterpret_cast<uint8_t *>(theta + cap);
+
+    const uint32_t w = blockIdx.x;
+    const int tid = threadIdx.x;
+    const size_t base = (size_t)w * cap;
+    const ObsSet &from = d.obs[cur];
+    const ObsSet &to = d.obs[cur ^ 1];
+    const int n = d.worldCount[w];
+    const int4 rb = d.rowBase[cur ^ 1][w];
+    const int off = d.worldOffset[w];
+    const float4 srew = d.speciesReward[w];
+
+    /* stage */
+    for (int s = tid; s < n; s += kExportThreads) {
+        const float4 p = d.pose[base + s];
+        const float4 sc = d.scratch[base + s];
+        ag[s].x = p.x; ag[s].y = p.y;
+        ag[s].oldrow = __float_as_int(sc.x);
+        theta[s] = view_yaw(Rot{p.z, p.w});
+        spec[s] = d.species[base + s];
+    }
+    __syncthreads();
+    /* new row = first row of (world, species) + rank among lower slots of the species */
+    for (int s = tid; s < n; s += kExportThreads) {
+        const int sp = spec[s];
+        int r = 0;
+        for (int j = 0; j < s; ++j) r += (spec[j] == sp);
+        const int row = comp(rb, sp - 1) + r;
+        ag[s].newrow = row;
+
+        /* updateObservations (:687-717), rewardSystem (:943-956), SensorOutputIndex (:783-784) */
+        const float4 sc = d.scratch[base + s];
+        const int hp = d.health[base + s];
+        const uint32_t st = (uint32_t)__float_as_int(sc.w);
+        reinterpret_cast<float2 *>(to.position)[row] = make_float2(ag[s].x, ag[s].y);
+        to.health[row] = (float)hp;
+        reinterpret_cast<float2 *>(to.surrounding)[row] = make_float2(sc.y, sc.z);
+        reinterpret_cast<int4 *>(to.stats)[row] = make_int4(st & 1u, (st >> 1) & 1u, (st >> 2) & 1u, (st >> 3) & 1u);
+        const float sterm = sp == 1 ? srew.x : sp == 2 ? srew.y : sp == 3 ? srew.z : srew.w;
+        to.reward[row] = with_sensors ? agent_reward(sterm, hp, (st & 4u) != 0, (st & 8u) != 0, (st & 2u) != 0) : 0.f;
+        d.sensorIndex[off + s] = row;
+        if (!with_sensors) d.target[base + s] = (int16_t)-1;
+    }
+    __syncthreads();
+
+    /* the sort: every column of the observation record follows its agent */
+    carry_column<int2, 3>(to.action, from.action, ag, n);
+    carry_column<int2, 3>(to.prev_action, from.prev_action, ag, n);
+    carry_column<float4, 4>(to.hidden, from.hidden, ag, n);
+    carry_column<float4, 4>(to.prev_hidden, from.prev_hidden, ag, n);
+    carry_column<int4, 1>(to.prev_stats, from.prev_stats, ag, n);
+    carry_column<float2, 1>(to.prev_position, from.prev_position, ag, n);
+    carry_column<float2, 1>(to.prev_surrounding, from.prev_surrounding, ag, n);
+    carry_column<float, 1>(to.prev_reward, from.prev_reward, ag, n);
+    carry_column<float, 1>(to.prev_health, from.prev_health, ag, n);
+    /* updateSensorOutputIdx (:774-780): last frame's sensor rows become the prev rows */
+    carry_column<int4, 2>(to.prev_semantic, from.semantic, ag, n);
+    carry_column<int4, 2>(to.prev_depth, from.depth, ag, n);
+
+    if (!with_sensors) return;
+
+    /* sensor: one warp per agent, one lane per ray */
+    const int lane = tid & 31, warp = tid >> 5;
+    for (int i = warp; i < n; i += kExportThreads / 32) {
+        const float ox = ag[i].x, oy = ag[i].y;
+        const Ray ray = make_ray(theta[i], lane);
+        float best = 0.f;
+        int hit = -1;
+        for (int j = 0; j < n; ++j) {
+            float t;
+            if (ray_sphere(ray, ox - ag[j].x, oy - ag[j].y, t)) {
+                if (t > kNearSphere && (hit < 0 || t < best)) { best = t; hit = j; }
+            }
+        }
+        const int row = ag[i].newrow;
+        uint8_t dep = hit >= 0 ? (uint8_t)(int)best : (uint8_t)255;
+        const int8_t sem = hit >= 0 ? (int8_t)spec[hit] : (int8_t)-1;
+        if (lane == 0) dep = (uint8_t)(uint32_t)row;          /* "sanity" overwrite (U9) */
+        to.depth[(size_t)row * kSensor + lane] = dep;
+        to.semantic[(size_t)row * kSensor + lane] = sem;
+        if (lane == kFinderRay) d.target[base + i] = (int16_t)hit;
+    }
+}
+
+/* ------------------------------------------------------------------------- */
+/* shift_kernel: cur -> prev for every row below totalAgents                   */
+
+__global__ void __launch_bounds__(256) shift_kernel(SimDev d, int cur)
+{
+    const ObsSet &o = d.obs[cur];
+    const size_t A = d.totals->totalAgents;
+    const size_t stride = (size_t)gridDim.x * blockDim.x;
+    const size_t t0 = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    /* hidden: 4 x 16 B per row */
+    {
+        const float4 *s = reinterpret_cast<const float4 *>(o.hidden);
+        float4 *p = reinterpret_cast<float4 *>(o.prev_hidden);
+        for (size_t i = t0; i < A * 4; i += stride) p[i] = s[i];
+    }
+    /* action: 24 B per row = 3 x 8 B; 2 rows = 3 x 16 B */
+    {
+        const int2 *s = reinterpret_cast<const int2 *>(o.action);
+        int2 *p = reinterpret_cast<int2 *>(o.prev_action);
+        for (size_t i = t0; i < A * 3; i += stride) p[i] = s[i];
+    }
+    /* stats, with the reference's field mix-up (src/sim/sim.cpp:1034, U7) */
+    {
+        const int4 *s = reinterpret_cast<const int4 *>(o.stats);
+        int4 *p = reinterpret_cast<int4 *>(o.prev_stats);
+        for (size_t i = t0; i < A; i += stride) { const int4 v = s[i]; p[i] = make_int4(v.x, v.x, v.z, v.w); }
+    }
+    {
+        const float2 *s = reinterpret_cast<const float2 *>(o.position);
+        float2 *p = reinterpret_cast<float2 *>(o.prev_position);
+        const float2 *s2 = reinterpret_cast<const float2 *>(o.surrounding);
+        float2 *p2 = reinterpret_cast<float2 *>(o.prev_surrounding);
+        for (size_t i = t0; i < A; i += stride) { p[i] = s[i]; p2[i] = s2[i]; }
+    }
+    for (size_t i = t0; i < A; i += stride) { o.prev_health[i] = o.health[i]; o.prev_reward[i] = o.reward[i]; }
+}
+
+/* ------------------------------------------------------------------------- */
+/* episode statistics and debug gathers (not on the hot path)                  */
+
+__global__ void stats_reduce_kernel(SimDev d, long long *out)
+{
+    __shared__ long long acc[16];
+    if (threadIdx.x < 16) acc[threadIdx.x] = 0;
+    __syncthreads();
+    long long l[14];
+    for (int k = 0; k < 14; ++k) l[k] = 0;
+    for (uint32_t w = threadIdx.x; w < d.numWorlds; w += blockDim.x) {
+        const int4 c = d.speciesCount[w], h = d.speciesHealth[w];
+        const WorldStats ws = d.wstats[w];
+        l[0] += c.x; l[1] += c.y; l[2] += c.z; l[3] += c.w;
+        l[4] += h.x; l[5] += h.y; l[6] += h.z; l[7] += h.w;
+        l[8] += ws.births; l[9] += ws.deaths; l[10] += ws.respawns; l[11] += ws.overflow;
+        l[12] += ws.eaten; l[13] += ws.shots;
+    }
+    for (int k = 0; k < 14; ++k) atomicAdd(reinterpret_cast<unsigned long long *>(&acc[2 + k]), (unsigned long long)l[k]);
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        acc[0] = (long long)d.totals->agentSteps;
+        acc[1] = (long long)d.totals->steps;
+    }
+    __syncthreads();
+    if (threadIdx.x < 16) out[threadIdx.x] = acc[threadIdx.x];
+}
+
+/* what: 0 pose (A,4) float, 1 health, 2 species, 3 target (A,1) int32; agent order */
+__global__ void debug_gather_kernel(SimDev d, int what, void *out)
+{
+    const uint32_t w = blockIdx.x;
+    const int n = d.worldCount[w], off = d.worldOffset[w];
+    const size_t base = (size_t)w * d.cap;
+    for (int s = threadIdx.x; s < n; s += blockDim.x) {
+        if (what == 0) reinterpret_cast<float4 *>(out)[off + s] = d.pose[base + s];
+        else if (what == 1) reinterpret_cast<int32_t *>(out)[off + s] = d.health[base + s];
+        else if (what == 2) reinterpret_cast<int32_t *>(out)[off + s] = d.species[base + s];
+        else reinterpret_cast<int32_t *>(out)[off + s] = d.target[base + s];
+    }
+}
+
+/* ------------------------------------------------------------------------- */
+/* launchers                                                                   */
+
+void launch_init(const SimDev &d, cudaStream_t s)
+{
+    uint32_t threads = d.cap < 64 ? 64 : d.cap;
+    init_kernel<<<d.numWorlds, threads, 0, s>>>(d);
+}
+
+void launch_step(const SimDev &d, int cur, cudaStream_t s)
+{
+    step_kernel<<<d.numWorlds, d.cap, step_smem_bytes(d.cap), s>>>(d, cur);
+}
+
+void launch_scan(const SimDev &d, int cur, int count_step, cudaStream_t s)
+{
+    scan_kernel<<<1, kScanThreads, 0, s>>>(d, cur, count_step);
+}
+
+void launch_export(const SimDev &d, int cur, int with_sensors, cudaStream_t s)
+{
+    export_kernel<<<d.numWorlds, kExportThreads, export_smem_bytes(d.cap), s>>>(d, cur, with_sensors);
+}
+
+void launch_shift(const SimDev &d, int cur, uint32_t rows_upper, cudaStream_t s)
+{
+    /* enough CTAs to cover the hidden-state column at one 16-B vector per thread, capped */
+    size_t vecs = (size_t)rows_upper * 4;
+    size_t blocks = (vecs + 255) / 256;
+    if (blocks > 148 * 16) blocks = 148 * 16;
+    if (blocks == 0) blocks = 1;
+    shift_kernel<<<(unsigned)blocks, 256, 0, s>>>(d, cur);
+}
+
+void launch_stats_reduce(const SimDev &d, long long *out16, cudaStream_t s)
+{
+    stats_reduce_kernel<<<1, 1024, 0, s>>>(d, out16);
+}
+
+void launch_debug_gather(const SimDev &d, int what, void *out, cudaStream_t s)
+{
+    debug_gather_kernel<<<d.numWorlds, 128, 0, s>>>(d, what, out);
+}
+
+} // namespace mbk

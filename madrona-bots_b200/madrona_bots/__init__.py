@@ -1,0 +1,202 @@
+"""madrona_bots -- drop-in replacement for the reference's nanobind module of the same name
+(src/entry/entry.cpp:16-44), backed by libmbots.so (hand-written sm_100a kernels).
+
+    from madrona_bots import SimManager
+    sim = SimManager(gpu_id, num_worlds, rand_seed, init_num_agents_per_world)
+    sim.step()
+    obs = sim.depth_tensor(False).to_torch()      # zero-copy CUDA view, (A, 32) uint8
+
+Same constructor, method names, tensor shapes and dtypes as the reference, so
+learn/training_loop.py and learn/env.py run against it unchanged. Rows are species-major;
+A (the leading dimension) is the live-agent count sampled when `*_tensor()` is called, so
+callers re-fetch the tensors after every step, exactly as with the reference
+(src/entry/mgr.cpp:70-76).
+"""
+import ctypes
+
+from . import _native
+from ._native import EXPORT
+
+__all__ = ["SimManager", "Tensor", "ScriptBotsViewer"]
+
+_TYPESTR = {0: "<i4", 1: "<f4", 2: "|i1", 3: "|u1"}
+_ITEMSIZE = {0: 4, 1: 4, 2: 1, 3: 1}
+
+
+class Tensor:
+    """madrona.Tensor look-alike (M/src/python/bindings.cpp:52-68): a typed, shaped device
+    pointer with `to_torch()` returning a zero-copy view on the simulator's GPU."""
+
+    def __init__(self, ptr, shape, dtype_code, gpu_id, owner):
+        self._ptr = ptr
+        self._shape = tuple(int(x) for x in shape)
+        self._code = dtype_code
+        self._gpu_id = gpu_id
+        self._owner = owner          # keeps the simulator (and its memory) alive
+
+    @property
+    def __cuda_array_interface__(self):
+        return {"shape": self._shape, "typestr": _TYPESTR[self._code], "data": (self._ptr, False),
+                "version": 2, "strides": None}
+
+    def shape(self):
+        return self._shape
+
+    def devicePtr(self):
+        return self._ptr
+
+    def isOnGPU(self):
+        return True
+
+    def gpuID(self):
+        return self._gpu_id
+
+    def to_torch(self):
+        import torch
+        dt = {0: torch.int32, 1: torch.float32, 2: torch.int8, 3: torch.uint8}[self._code]
+        dev = torch.device("cuda", self._gpu_id)
+        if self._shape[0] == 0:
+            return torch.empty(self._shape, dtype=dt, device=dev)
+        t = torch.as_tensor(self, device=dev)
+        assert t.data_ptr() == self._ptr, "expected a zero-copy view"
+        return t
+
+
+class SimManager:
+    """Mirror of `Manager` as bound by the reference (src/entry/entry.cpp:16-44,
+    src/entry/mgr.hpp:28-62)."""
+
+    def __init__(self, gpu_id, num_worlds, rand_seed, init_num_agents_per_world, *,
+                 max_agents_per_world=0, world_id_offset=0):
+        self._lib = _native.lib()
+        self._h = ctypes.c_void_p()
+        self._gpu_id = int(gpu_id)
+        self.num_worlds = int(num_worlds)
+        cfg = _native.Config(int(gpu_id), int(num_worlds), int(rand_seed) & 0xFFFFFFFF,
+                             int(init_num_agents_per_world), int(max_agents_per_world), int(world_id_offset))
+        _native.check(self._lib.mbots_create_ex(ctypes.byref(cfg), ctypes.byref(self._h)), "mbots_create_ex")
+
+    def __del__(self):
+        h = getattr(self, "_h", None)
+        if h is not None and h.value:
+            self._lib.mbots_destroy(h)
+            self._h = ctypes.c_void_p()
+
+    def _stream(self):
+        import torch
+        return ctypes.c_void_p(torch.cuda.current_stream(self._gpu_id).cuda_stream)
+
+    # ---- Manager::step / shiftObservations ------------------------------------------------
+    def step(self):
+        _native.check(self._lib.mbots_step(self._h, self._stream()), "mbots_step")
+
+    def step_async(self):
+        _native.check(self._lib.mbots_step_async(self._h, self._stream()), "mbots_step_async")
+
+    def sync(self):
+        _native.check(self._lib.mbots_sync(self._h, self._stream()), "mbots_sync")
+
+    def shift_observations(self):
+        _native.check(self._lib.mbots_shift_observations(self._h, self._stream()), "mbots_shift_observations")
+
+    def shift_observations_async(self):
+        _native.check(self._lib.mbots_shift_observations_async(self._h, self._stream()),
+                      "mbots_shift_observations_async")
+
+    # ---- exports --------------------------------------------------------------------------
+    def export(self, name):
+        ptr = ctypes.c_void_p()
+        dims = (ctypes.c_int64 * 2)()
+        dt = ctypes.c_int32()
+        _native.check(self._lib.mbots_tensor(self._h, EXPORT[name], ctypes.byref(ptr), dims, ctypes.byref(dt)),
+                      f"mbots_tensor({name})")
+        return Tensor(ptr.value or 0, (dims[0], dims[1]), dt.value, self._gpu_id, self)
+
+    def _pair(self, cur, prev, is_prev):
+        return self.export(prev if is_prev else cur)
+
+    def depth_tensor(self, is_prev=False):
+        return self._pair("SENSOR_DEPTH", "PREV_SENSOR_DEPTH", is_prev)
+
+    def semantic_tensor(self, is_prev=False):
+        return self._pair("SENSOR_SEMANTIC", "PREV_SENSOR_SEMANTIC", is_prev)
+
+    def reward_tensor(self, is_prev=False):
+        return self._pair("REWARD", "PREV_REWARD", is_prev)
+
+    def species_count_tensor(self):
+        return self.export("SPECIES_COUNT")
+
+    def position_tensor(self, is_prev=False):
+        return self._pair("POSITION", "PREV_POSITION", is_prev)
+
+    def health_tensor(self, is_prev=False):
+        return self._pair("HEALTH", "PREV_HEALTH", is_prev)
+
+    def surrounding_tensor(self, is_prev=False):
+        return self._pair("SURROUNDING", "PREV_SURROUNDING", is_prev)
+
+    def action_tensor(self, is_prev=False):
+        return self._pair("ACTION", "PREV_ACTION", is_prev)
+
+    def stats_tensor(self, is_prev=False):
+        return self._pair("STATS", "PREV_STATS", is_prev)
+
+    def hidden_state_tensor(self, is_prev=False):
+        return self._pair("HIDDEN_STATE", "PREV_HIDDEN_STATE", is_prev)
+
+    # C++-only members of the reference's Manager (src/entry/mgr.cpp:241-277)
+    def sensor_index_tensor(self):
+        return self.export("SENSOR_INDEX")
+
+    def set_action(self, agent_idx, forward, backward, rotate_left, rotate_right, shoot, breed):
+        _native.check(self._lib.mbots_set_action(self._h, agent_idx, forward, backward, rotate_left,
+                                                 rotate_right, shoot, breed), "mbots_set_action")
+
+    def agent_offset_for_world(self, world_idx):
+        out = ctypes.c_uint32()
+        _native.check(self._lib.mbots_agent_offset_for_world(self._h, world_idx, ctypes.byref(out)),
+                      "mbots_agent_offset_for_world")
+        return out.value
+
+    # ---- extensions -----------------------------------------------------------------------
+    def num_agents(self):
+        out = ctypes.c_uint32()
+        _native.check(self._lib.mbots_num_agents(self._h, ctypes.byref(out)), "mbots_num_agents")
+        return out.value
+
+    def episode_stats(self):
+        out = (ctypes.c_int64 * 16)()
+        _native.check(self._lib.mbots_episode_stats(self._h, out, self._stream()), "mbots_episode_stats")
+        return list(out)
+
+    def launch_count(self):
+        out = ctypes.c_uint64()
+        _native.check(self._lib.mbots_launch_count(self._h, ctypes.byref(out)), "mbots_launch_count")
+        return out.value
+
+    def profile(self, enable):
+        _native.check(self._lib.mbots_profile(self._h, 1 if enable else 0), "mbots_profile")
+
+    def profile_read(self):
+        ms = (ctypes.c_float * 4)()
+        calls = (ctypes.c_uint32 * 4)()
+        _native.check(self._lib.mbots_profile_read(self._h, ms, calls), "mbots_profile_read")
+        names = ("step", "scan", "export_sense", "shift")
+        return {n: {"ms": ms[i], "calls": calls[i]} for i, n in enumerate(names)}
+
+    def copy_from_host(self, name, host_ptr, nbytes):
+        _native.check(self._lib.mbots_copy_from_host(self._h, EXPORT[name], ctypes.c_void_p(host_ptr), nbytes,
+                                                     self._stream()), "mbots_copy_from_host")
+
+    def copy_to_host(self, name, host_ptr, nbytes):
+        _native.check(self._lib.mbots_copy_to_host(self._h, EXPORT[name], ctypes.c_void_p(host_ptr), nbytes,
+                                                   self._stream()), "mbots_copy_to_host")
+
+
+class ScriptBotsViewer:
+    """The reference's Vulkan viewer (src/gfx, src/entry/entry.cpp:46-80). Unavailable on this
+    box: there is no graphics stack here or on the GPU machines (out of scope)."""
+
+    def __init__(self, *args, **kwargs):
+        raise RuntimeError("ScriptBotsViewer needs a Vulkan graphics stack: unavailable on this box")
