@@ -104,6 +104,8 @@ int alloc_all(mbots_sim *s)
     ALLOC(d.worldCount, W); ALLOC(d.worldOffset, W); ALLOC(d.rngKey, W); ALLOC(d.rngCount, W);
     ALLOC(d.numFood, W); ALLOC(d.food, W * 48);
     ALLOC(d.speciesLive, W); ALLOC(d.rowBase[0], W); ALLOC(d.rowBase[1], W);
+    const size_t tiles = (W + kScanTile - 1) / kScanTile;
+    ALLOC(d.tileSum[0], tiles); ALLOC(d.tileSum[1], tiles);
     ALLOC(d.speciesCount, W); ALLOC(d.speciesReward, W); ALLOC(d.speciesHealth, W); ALLOC(d.wstats, W);
     ALLOC(d.sensorIndex, rows); ALLOC(d.done, rows); ALLOC(d.reset, W);
     ALLOC(d.totals, 1);
@@ -155,7 +157,16 @@ int enqueue_repack(mbots_sim *s, cudaStream_t st, int with_sensors, int count_st
 int enqueue_step(mbots_sim *s, cudaStream_t st)
 {
     if (s->profile) cudaEventRecord(s->ev[0], st);
-    launch_step(s->d, s->cur, st);
+    /* block size: the largest world known from the last synchronised step (rounded to a warp), or
+     * the capacity when counts are stale because steps were enqueued without a sync in between */
+    uint32_t threads = s->d.cap;
+    if (!s->dirty) {
+        uint32_t need = s->hTotals->maxWorldCount;
+        if (need < s->d.initAgents) need = s->d.initAgents;
+        if (need < 32u) need = 32u;
+        threads = (need + 31u) & ~31u;
+    }
+    launch_step(s->d, s->cur, threads, st);
     if (s->profile) cudaEventRecord(s->ev[1], st);
     s->launches += 1;
     int rc = enqueue_repack(s, st, 1, 1);

@@ -33,9 +33,13 @@ struct ObsSet {
 /* Per-world cumulative event counters (episode statistics). */
 struct WorldStats { uint32_t births, deaths, respawns, overflow, eaten, shots, pad0, pad1; };
 
+/* Partial sums of the row scan over one tile of kScanTile consecutive worlds. */
+constexpr int kScanTile = 1024;
+struct TileSum { int c[4]; int maxCount; int pad[3]; };
+
 struct Totals {
     uint32_t totalAgents;     /* SimBridge::totalNumAgents */
-    uint32_t pad;
+    uint32_t maxWorldCount;   /* most agents in any world */
     unsigned long long agentSteps, steps;
     uint32_t speciesTotal[4]; /* rows per species block */
 };
@@ -58,6 +62,7 @@ struct SimDev {
     int32_t *numFood;         /* Sim::currentNumFood */
     uint2 *food;              /* [numWorlds * 48]: byte p<5 = (x<<4|y) of package p, byte 5 = has-food mask */
     int4 *speciesLive;        /* rows per (world, species) after respawn: input of the row scan */
+    TileSum *tileSum[2];      /* per-tile sums of speciesLive, accumulated by the step that owns parity `cur` */
     int4 *rowBase[2];         /* first row of (world, species) in obs set 0 / 1 */
     int4 *speciesCount;       /* export SpeciesCount (tracker counts, before respawn) */
     float4 *speciesReward;    /* SpeciesReward */
@@ -74,7 +79,7 @@ struct SimDev {
 
 /* launchers (sim_kernels.cu) */
 void launch_init(const SimDev &d, cudaStream_t s);
-void launch_step(const SimDev &d, int cur, cudaStream_t s);
+void launch_step(const SimDev &d, int cur, uint32_t threads, cudaStream_t s);
 void launch_scan(const SimDev &d, int cur, int count_step, cudaStream_t s);
 void launch_export(const SimDev &d, int cur, int with_sensors, cudaStream_t s);
 void launch_shift(const SimDev &d, int cur, uint32_t rows_upper, cudaStream_t s);

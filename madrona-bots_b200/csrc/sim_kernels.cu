@@ -34,25 +34,9 @@ using namespace mbp;
 /* ------------------------------------------------------------------------- */
 /* small block-level helpers                                                   */
 
-/* Exclusive scan of a 0/1 flag over the CTA in thread order. `wc` is a shared int[32].
- * Contains two barriers; must be called by every thread of the CTA. */
-__device__ __forceinline__ int block_scan_flag(bool flag, int &total, int *wc)
-{
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nw = (blockDim.x + 31) >> 5;
-    const unsigned b = __ballot_sync(FULL, flag);
-    const int in_warp = __popc(b & ((1u << lane) - 1u));
-    if (lane == 0) wc[warp] = __popc(b);
-    __syncthreads();
-    int base = 0, tot = 0;
-    for (int i = 0; i < nw; ++i) { const int c = wc[i]; if (i < warp) base += c; tot += c; }
-    __syncthreads();
-    total = tot;
-    return base + in_warp;
-}
-
 /* Rank of this thread among lower threads of the same species (sp in 0..3, or -1 for
  * "not an agent"), and the per-species totals. `wc` is a shared uint32[32] (8 bits per
- * species per warp). Two barriers. */
+ * species per warp), written once per kernel. One barrier. */
 __device__ __forceinline__ int block_species_rank(int sp, int tot[4], uint32_t *wc)
 {
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nw = (blockDim.x + 31) >> 5;
@@ -78,7 +62,6 @@ __device__ __forceinline__ int block_species_rank(int sp, int tot[4], uint32_t *
             if (i < warp && sp == k) base += c;
         }
     }
-    __syncthreads();
     return base + in_warp;
 }
 
@@ -115,6 +98,9 @@ __global__ void init_kernel(SimDev d)
         const int q = (int)(d.initAgents / kNumSpecies), r = (int)(d.initAgents % kNumSpecies);
         c.x = q + (r > 0); c.y = q + (r > 1); c.z = q + (r > 2); c.w = q;
         d.speciesLive[w] = c;
+        TileSum *ts = d.tileSum[0] + (w / kScanTile);
+        atomicAdd(&ts->c[0], c.x); atomicAdd(&ts->c[1], c.y); atomicAdd(&ts->c[2], c.z); atomicAdd(&ts->c[3], c.w);
+        atomicMax(&ts->maxCount, (int)d.initAgents);
         d.speciesCount[w] = make_int4(0, 0, 0, 0);
         d.speciesReward[w] = make_float4(0.f, 0.f, 0.f, 0.f);
         d.speciesHealth[w] = make_int4(0, 0, 0, 0);
@@ -131,8 +117,8 @@ struct StepShared {
     uint32_t chunkSpeed[kNumChunks];
     uint2 food[kNumChunks];
     Key draws[32];
-    int wc[32];
     uint32_t wcs[32];
+    uint32_t xch0[32], xch1[32];
     uint32_t cnt[4], hsum[4];
     uint32_t rngCount;
     int32_t numFood;
@@ -207,12 +193,14 @@ __global__ void step_kernel(SimDev d, int cur)
     uint8_t *spec = reinterpret_cast<uint8_t *>(ateMask + cap / 32);
 
     const uint32_t w = blockIdx.x;
-    const uint32_t s = threadIdx.x;
+    const uint32_t s = threadIdx.x;                    /* blockDim >= max(live agents, initAgents, 32) */
+    const int lane = s & 31, warp = s >> 5, nw = (blockDim.x + 31) >> 5;
     const size_t base = (size_t)w * cap;
     const ObsSet &from = d.obs[cur];
 
     /* ---- P0: stage the world ---- */
     const int n0 = d.worldCount[w];
+    const int4 rb0 = d.rowBase[cur][w];
     const bool active = (int)s < n0;
     float4 pose = make_float4(0.f, 0.f, 1.f, 0.f);
     int hp = 0, sp = 0, tgt = -1;
@@ -230,10 +218,9 @@ __global__ void step_kernel(SimDev d, int cur)
         sh.chunkSpeed[c] = 0;
         sh.food[c] = d.food[(size_t)w * kNumChunks + c];
     }
-    uint32_t rng0 = 0;
     if (s < 32) {
         const uint2 kk = d.rngKey[w];
-        rng0 = d.rngCount[w];
+        const uint32_t rng0 = d.rngCount[w];
         sh.draws[s] = key_split(Key{kk.x, kk.y}, rng0 + s);
         if (s < 4) { sh.cnt[s] = 0; sh.hsum[s] = 0; }
         if (s == 0) {
@@ -244,11 +231,11 @@ __global__ void step_kernel(SimDev d, int cur)
     }
     /* the agent's observation row in set `cur` (rank among lower slots of its species) */
     int tot0[4];
-    const int rank0 = block_species_rank(active ? sp - 1 : -1, tot0, sh.wcs);   /* barriers */
+    const int rank0 = block_species_rank(active ? sp - 1 : -1, tot0, sh.wcs);   /* barrier B1 */
     int act[6] = {0, 0, 0, 0, 0, 0};
     int oldrow = -1;
     if (active) {
-        oldrow = comp(d.rowBase[cur][w], sp - 1) + rank0;
+        oldrow = comp(rb0, sp - 1) + rank0;
         const int2 *ap = reinterpret_cast<const int2 *>(from.action + (size_t)oldrow * 6);
         const int2 a0 = ap[0], a1 = ap[1], a2 = ap[2];
         act[0] = a0.x; act[1] = a0.y; act[2] = a1.x; act[3] = a1.y; act[4] = a2.x; act[5] = a2.y;
@@ -270,20 +257,56 @@ __global__ void step_kernel(SimDev d, int cur)
         atomicAdd(&sh.chunkAgents[c], 1u);
         atomicAdd(&sh.chunkSpeed[c], (uint32_t)(len * 2.f));
     }
-    __syncthreads();
+    __syncthreads();                                   /* barrier B2 */
 
-    /* ---- P2: healthSync (:505-581) ---- */
-    hp = accum[s];
+    /* ---- P2: healthSync (:505-581), speciesTrackerUpdate (:719-734) ----
+     * Common case (nobody stands on food, no slot overflow): one barrier. Breed / live flags,
+     * the any-agent-on-food vote and the warp counts for the two compaction scans all travel
+     * in one shared word per warp; the tracker sums are shared-memory atomics issued before it. */
+    const int hp0 = accum[s];
     const int mychunk = active ? chunk_of(pose.x, pose.y) : 0;
     const uint32_t mycell = cell_of(pose.x, pose.y);
     const bool wants = active && food_match(sh.food[mychunk], mycell) != 0;
-    if (__syncthreads_or(wants)) {
-        /* Rare: at least one agent stands on food. Resolve in slot order so that the lowest
-         * slot wins a contested package (FoodPackage::consume CAS race, sim.inl:76-99; U11). */
+    const bool canBreed = active && act[5] && tgt >= 0 && spec[tgt] == sp;
+    const int room = (int)cap - n0;                    /* makeAgent fails once the slot table is full (D1) */
+    const unsigned lt = (1u << lane) - 1u;
+
+    bool breeds, live;
+    int nBreed = 0, nLive = 0, bidx = 0, lidx = 0;
+    bool ate = false;
+    for (int round = 0;; ++round) {
+        hp = hp0 + (ate ? 20 : 0);
+        breeds = canBreed && hp > 10;
+        if (breeds) hp -= 40;
+        live = active && hp > 0;
+        const unsigned bb = __ballot_sync(FULL, breeds), bl = __ballot_sync(FULL, live);
+        const unsigned bw = __ballot_sync(FULL, wants);
+        uint32_t *xch = round == 0 ? sh.xch0 : sh.xch1;
+        if (lane == 0) xch[warp] = (uint32_t)__popc(bb) | ((uint32_t)__popc(bl) << 8) | (bw && round == 0 ? 1u << 31 : 0u);
+        if (live) { atomicAdd(&sh.cnt[sp - 1], 1u); atomicAdd(&sh.hsum[sp - 1], (uint32_t)hp); }
+        if (breeds) { atomicAdd(&sh.cnt[sp - 1], 1u); atomicAdd(&sh.hsum[sp - 1], 50u); }   /* newborn, if it fits */
+        __syncthreads();                               /* barrier B3 */
+        bool anyWants = false;
+        int bbase = 0, lbase = 0;
+        nBreed = nLive = 0;
+        for (int i = 0; i < nw; ++i) {
+            const uint32_t v = xch[i];
+            const int cb = (int)(v & 0xffu), cl = (int)((v >> 8) & 0xffu);
+            if (i < warp) { bbase += cb; lbase += cl; }
+            nBreed += cb; nLive += cl;
+            anyWants |= (v >> 31) != 0;
+        }
+        bidx = bbase + __popc(bb & lt);
+        lidx = lbase + __popc(bl & lt);
+        if (!anyWants) break;
+        /* Rare: at least one agent stands on food. Resolve in slot order so that the lowest slot
+         * wins a contested package (FoodPackage::consume CAS race, sim.inl:76-99; U11), then redo
+         * the round with the +20 applied. */
         if (wants) {
             wantKey[s] = ((uint32_t)mychunk << 8) | mycell;
             atomicOr(&wantMask[s >> 5], 1u << (s & 31));
         }
+        if (s < 4) { sh.cnt[s] = 0; sh.hsum[s] = 0; }
         __syncthreads();
         if (s == 0) {
             for (uint32_t wd = 0; wd < cap / 32; ++wd) {
@@ -307,29 +330,20 @@ __global__ void step_kernel(SimDev d, int cur)
             }
         }
         __syncthreads();
-        if (active && (ateMask[s >> 5] >> (s & 31) & 1u)) { hp += 20; stat |= 4u; }
+        ate = active && ((ateMask[s >> 5] >> (s & 31)) & 1u);
     }
-    bool breeds = false;
-    if (active && act[5] && hp > 10 && tgt >= 0 && spec[tgt] == sp) {
-        hp -= 40;
-        stat |= 8u;
-        breeds = true;
-    }
-    const bool live = active && hp > 0;
-    int nBreed, nLive;
-    const int bidx = block_scan_flag(breeds, nBreed, sh.wc);
-    const int lidx = block_scan_flag(live, nLive, sh.wc);
-    const int room = (int)cap - n0;                    /* makeAgent fails once the slot table is full (D1) */
+    if (ate) stat |= 4u;
+    if (breeds) stat |= 8u;
     const int bornOk = nBreed < room ? nBreed : room;
     const bool childOk = breeds && bidx < room;
+    if (nBreed > room) {                               /* rare: take back the newborns that did not fit */
+        if (breeds && !childOk) { atomicSub(&sh.cnt[sp - 1], 1u); atomicSub(&sh.hsum[sp - 1], 50u); }
+        __syncthreads();
+    }
 
     /* updateSurroundingObservation (:583-654); a newborn shares its parent's position */
     float sn = 0.f, ss = 0.f;
     if (live || childOk) surroundings(pose.x, pose.y, sh.chunkAgents, sh.chunkSpeed, sn, ss);
-
-    /* speciesTrackerUpdate (:719-734) */
-    if (live) { atomicAdd(&sh.cnt[sp - 1], 1u); atomicAdd(&sh.hsum[sp - 1], (uint32_t)hp); }
-    if (childOk) { atomicAdd(&sh.cnt[sp - 1], 1u); atomicAdd(&sh.hsum[sp - 1], 50u); }
 
     /* compaction: survivors keep their order, then newborns in parent order (U11) */
     if (live) {
@@ -346,7 +360,6 @@ __global__ void step_kernel(SimDev d, int cur)
         d.species[o] = (uint8_t)sp;
         d.scratch[o] = make_float4(__int_as_float(-1), sn, ss, __int_as_float(0));
     }
-    __syncthreads();
 
     /* ---- P3: speciesInfoSync + respawn (:791-838) ---- */
     const uint32_t q = d.initAgents / kNumSpecies;
@@ -390,13 +403,19 @@ __global__ void step_kernel(SimDev d, int cur)
             lr[k] = (int)(c4[k] + ok);
             rwp[k] = species_reward(c4[k], sh.hsum[k], d.initAgents);
         }
+        const int count1 = nLive + bornOk + (int)respOk;
         d.speciesLive[w] = liveRows;
         d.speciesCount[w] = make_int4((int)c4[0], (int)c4[1], (int)c4[2], (int)c4[3]);
         d.speciesHealth[w] = make_int4((int)sh.hsum[0], (int)sh.hsum[1], (int)sh.hsum[2], (int)sh.hsum[3]);
         d.speciesReward[w] = rw;
-        d.worldCount[w] = nLive + bornOk + (int)respOk;
+        d.worldCount[w] = count1;
         d.rngCount[w] = rngBase + 2u * needTotal;
         d.numFood[w] = sh.numFood;
+        /* partial sums of the row scan: one tile = kScanTile consecutive worlds */
+        TileSum *ts = d.tileSum[cur] + (w / kScanTile);
+#pragma unroll
+        for (int k = 0; k < 4; ++k) if (lr[k]) atomicAdd(&ts->c[k], lr[k]);
+        atomicMax(&ts->maxCount, count1);
         const uint32_t deaths = (uint32_t)(n0 - nLive);
         const uint32_t overflow = (uint32_t)(nBreed - bornOk) + (needTotal - respOk);
         if (bornOk | (int)deaths | (int)respOk | (int)overflow | (int)sh.eaten | (int)sh.shots) {
@@ -413,7 +432,7 @@ __global__ void step_kernel(SimDev d, int cur)
 /* ------------------------------------------------------------------------- */
 /* scan_kernel: rows are ordered (species, world, slot). One CTA. */
 
-constexpr int kScanThreads = 1024;
+static_assert(kScanTile == 1024, "one thread per world of a tile");
 
 __device__ __forceinline__ int warp_incl_scan(int v)
 {
@@ -426,72 +445,80 @@ __device__ __forceinline__ int warp_incl_scan(int v)
     return v;
 }
 
-__global__ void __launch_bounds__(kScanThreads) scan_kernel(SimDev d, int cur, int count_step)
+/* One CTA per tile of 1,024 worlds, no inter-CTA dependency: the per-tile partial sums were
+ * accumulated by step_kernel (tileSum[cur]); every CTA reduces them to the species totals and to
+ * the prefix of its own tile, then scans its worlds. Also zeroes tileSum[cur ^ 1] for the next step. */
+__global__ void __launch_bounds__(kScanTile) scan_kernel(SimDev d, int cur, int count_step)
 {
-    __shared__ int red[32][4];
+    __shared__ int red[32][9];
+    __shared__ int fin[9];
     __shared__ int wsum[32][5];
-    __shared__ int carry[5];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const int W = (int)d.numWorlds;
+    const int W = (int)d.numWorlds, tile = blockIdx.x, nt = gridDim.x;
+    const TileSum *ts = d.tileSum[cur];
 
-    /* pass 1: rows per species */
-    int t4[4] = {0, 0, 0, 0};
-    for (int w = tid; w < W; w += kScanThreads) {
-        const int4 c = d.speciesLive[w];
-        t4[0] += c.x; t4[1] += c.y; t4[2] += c.z; t4[3] += c.w;
+    int v9[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0};           /* totals[4], prefix of this tile[4], max count */
+    for (int t = tid; t < nt; t += kScanTile) {
+        const TileSum x = ts[t];
+#pragma unroll
+        for (int k = 0; k < 4; ++k) { v9[k] += x.c[k]; if (t < tile) v9[4 + k] += x.c[k]; }
+        v9[8] = max(v9[8], x.maxCount);
     }
 #pragma unroll
-    for (int k = 0; k < 4; ++k) {
-        int v = t4[k];
+    for (int k = 0; k < 9; ++k) {
+        int v = v9[k];
 #pragma unroll
-        for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(FULL, v, o);
+        for (int o = 16; o > 0; o >>= 1) {
+            const int u = __shfl_xor_sync(FULL, v, o);
+            v = k == 8 ? max(v, u) : v + u;
+        }
         if (lane == 0) red[warp][k] = v;
     }
-    __syncthreads();
-    if (tid == 0) {
-        int tot[4] = {0, 0, 0, 0};
-        for (int i = 0; i < kScanThreads / 32; ++i)
-            for (int k = 0; k < 4; ++k) tot[k] += red[i][k];
-        int b = 0;
-        for (int k = 0; k < 4; ++k) { carry[k] = b; b += tot[k]; d.totals->speciesTotal[k] = (uint32_t)tot[k]; }
-        carry[4] = 0;
-        d.totals->totalAgents = (uint32_t)b;
-        if (count_step) { d.totals->agentSteps += (unsigned long long)b; d.totals->steps += 1ull; }
+    const int w = tile * kScanTile + tid;
+    int4 c = make_int4(0, 0, 0, 0);
+    if (w < W) c = d.speciesLive[w];
+    int v[5] = {c.x, c.y, c.z, c.w, c.x + c.y + c.z + c.w};
+    int inc[5];
+#pragma unroll
+    for (int k = 0; k < 5; ++k) {
+        inc[k] = warp_incl_scan(v[k]);
+        if (lane == 31) wsum[warp][k] = inc[k];
     }
     __syncthreads();
-
-    /* pass 2: tile-wise exclusive scan with a running carry */
-    int4 *rb = d.rowBase[cur ^ 1];
-    for (int w0 = 0; w0 < W; w0 += kScanThreads) {
-        const int w = w0 + tid;
-        int4 c = make_int4(0, 0, 0, 0);
-        if (w < W) c = d.speciesLive[w];
-        int v[5] = {c.x, c.y, c.z, c.w, c.x + c.y + c.z + c.w};
-        int inc[5];
+    if (tid < 9) {
+        int a = 0;
+        for (int i = 0; i < kScanTile / 32; ++i) a = tid == 8 ? max(a, red[i][tid]) : a + red[i][tid];
+        fin[tid] = a;
+    }
+    __syncthreads();
+    int base[5];
+    int spBase = 0, agentsBefore = 0;
 #pragma unroll
-        for (int k = 0; k < 5; ++k) {
-            inc[k] = warp_incl_scan(v[k]);
-            if (lane == 31) wsum[warp][k] = inc[k];
-        }
-        __syncthreads();
-        int basek[5];
+    for (int k = 0; k < 4; ++k) {
+        base[k] = spBase + fin[4 + k];                 /* species block start + rows of earlier tiles */
+        spBase += fin[k];
+        agentsBefore += fin[4 + k];
+    }
+    base[4] = agentsBefore;
 #pragma unroll
-        for (int k = 0; k < 5; ++k) {
-            int b = carry[k];
-            for (int i = 0; i < warp; ++i) b += wsum[i][k];
-            basek[k] = b;
+    for (int k = 0; k < 5; ++k) {
+        int b = base[k];
+        for (int i = 0; i < warp; ++i) b += wsum[i][k];
+        base[k] = b + inc[k] - v[k];
+    }
+    if (w < W) {
+        d.rowBase[cur ^ 1][w] = make_int4(base[0], base[1], base[2], base[3]);
+        d.worldOffset[w] = base[4];
+    }
+    if (tile == 0) {
+        TileSum z = {{0, 0, 0, 0}, 0, {0, 0, 0}};
+        for (int t = tid; t < nt; t += kScanTile) d.tileSum[cur ^ 1][t] = z;
+        if (tid == 0) {
+            for (int k = 0; k < 4; ++k) d.totals->speciesTotal[k] = (uint32_t)fin[k];
+            d.totals->totalAgents = (uint32_t)spBase;
+            d.totals->maxWorldCount = (uint32_t)fin[8];
+            if (count_step) { d.totals->agentSteps += (unsigned long long)spBase; d.totals->steps += 1ull; }
         }
-        if (w < W) {
-            rb[w] = make_int4(basek[0] + inc[0] - v[0], basek[1] + inc[1] - v[1],
-                              basek[2] + inc[2] - v[2], basek[3] + inc[3] - v[3]);
-            d.worldOffset[w] = basek[4] + inc[4] - v[4];
-        }
-        __syncthreads();
-        if (tid == kScanThreads - 1) {
-#pragma unroll
-            for (int k = 0; k < 5; ++k) carry[k] = basek[k] + inc[k];
-        }
-        __syncthreads();
     }
 }
 
@@ -502,9 +529,12 @@ constexpr int kExportThreads = 128;
 
 struct ExportAgent { float x, y; int newrow, oldrow; };
 
+constexpr int kSenseTile = 32;   /* observers per sensor pass: 32 x 32 rays x (16 + 8) B of shared memory */
+
 size_t export_smem_bytes(uint32_t cap)
 {
-    return (size_t)cap * (sizeof(ExportAgent) + 4 /*theta*/ + 1 /*species*/) + 16;
+    return (size_t)kSenseTile * kSensor * (sizeof(float4) + sizeof(unsigned long long)) +
+           (size_t)cap * (sizeof(ExportAgent) + 4 /*theta*/ + 1 /*species*/) + 16;
 }
 
 /* Copy one column of every agent of the world from its old row to its new row.
@@ -529,7 +559,9 @@ __global__ void __launch_bounds__(kExportThreads) export_kernel(SimDev d, int cu
 {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     const uint32_t cap = d.cap;
-    ExportAgent *ag = reinterpret_cast<ExportAgent *>(smem_raw);
+    float4 *rays = reinterpret_cast<float4 *>(smem_raw);
+    unsigned long long *best = reinterpret_cast<unsigned long long *>(rays + kSenseTile * kSensor);
+    ExportAgent *ag = reinterpret_cast<ExportAgent *>(best + kSenseTile * kSensor);
     float *theta = reinterpret_cast<float *>(ag + cap);
     uint8_t *spec = reinterpret_cast<uint8_t *>(theta + cap);
 
@@ -592,26 +624,58 @@ __global__ void __launch_bounds__(kExportThreads) export_kernel(SimDev d, int cu
 
     if (!with_sensors) return;
 
-    /* sensor: one warp per agent, one lane per ray */
-    const int lane = tid & 31, warp = tid >> 5;
-    for (int i = warp; i < n; i += kExportThreads / 32) {
-        const float ox = ag[i].x, oy = ag[i].y;
-        const Ray ray = make_ray(theta[i], lane);
-        float best = 0.f;
-        int hit = -1;
-        for (int j = 0; j < n; ++j) {
-            float t;
-            if (ray_sphere(ray, ox - ag[j].x, oy - ag[j].y, t)) {
-                if (t > kNearSphere && (hit < 0 || t < best)) { best = t; hit = j; }
+    /* Sensor (M/src/mw/device/bvh_raycast.cpp:193-305), agents in tiles of kSenseTile:
+     *  1. one thread per (agent, ray): ray direction + quadratic constants -> shared memory
+     *  2. one thread per (agent, target) pair: conservative candidate rays (pair_candidates),
+     *     exact ray/sphere test on those only, nearest accepted hit kept with a 64-bit
+     *     shared-memory atomicMin on (t bits << 32 | target slot)  -- ties go to the lowest slot
+     *  3. one thread per (agent, ray): decode, write depth / semantic bytes and the finder hit */
+    for (int tile0 = 0; tile0 < n; tile0 += kSenseTile) {
+        const int m = min(kSenseTile, n - tile0);
+        for (int idx = tid; idx < m * kSensor; idx += kExportThreads) {
+            const Ray r = make_ray(theta[tile0 + (idx >> 5)], idx & 31);
+            rays[idx] = make_float4(r.dx, r.dy, r.a4, r.a2);
+            best[idx] = ~0ull;
+        }
+        __syncthreads();
+        const int pairs = m * n;
+        for (int p = tid; p < pairs; p += kExportThreads) {
+            const int il = p / n, j = p - il * n, i = tile0 + il;
+            const float ocx = ag[i].x - ag[j].x, ocy = ag[i].y - ag[j].y;
+            RaySpan sp;
+            if (!pair_candidates(ocx, ocy, theta[i], sp)) continue;
+            const float c = (ocx * ocx + ocy * ocy) - 1.f;
+            /* one loop over both fans: forward rays flo..fhi, then backward rays 24+blo..24+bhi */
+            int r = sp.flo <= sp.fhi ? sp.flo : kFwdRays + sp.blo;
+            const int rend = sp.blo <= sp.bhi ? kFwdRays + sp.bhi : sp.fhi;
+            while (r <= rend) {
+                const float4 q = rays[il * kSensor + r];
+                const float bq = 2.0f * (ocx * q.x + ocy * q.y);
+                const float disc = bq * bq - q.z * c;
+                if (disc >= 0.f) {
+                    const float t = (-bq - sqrtf(disc)) / q.w;
+                    if (t > kNearSphere)
+                        atomicMin(&best[il * kSensor + r],
+                                  ((unsigned long long)__float_as_uint(t) << 32) | (unsigned long long)(uint32_t)j);
+                }
+                r = (r == sp.fhi && r < kFwdRays) ? kFwdRays + sp.blo : r + 1;
             }
         }
-        const int row = ag[i].newrow;
-        uint8_t dep = hit >= 0 ? (uint8_t)(int)best : (uint8_t)255;
-        const int8_t sem = hit >= 0 ? (int8_t)spec[hit] : (int8_t)-1;
-        if (lane == 0) dep = (uint8_t)(uint32_t)row;          /* "sanity" overwrite (U9) */
-        to.depth[(size_t)row * kSensor + lane] = dep;
-        to.semantic[(size_t)row * kSensor + lane] = sem;
-        if (lane == kFinderRay) d.target[base + i] = (int16_t)hit;
+        __syncthreads();
+        for (int idx = tid; idx < m * kSensor; idx += kExportThreads) {
+            const int i = tile0 + (idx >> 5), ray = idx & 31;
+            const unsigned long long key = best[idx];
+            const bool hit = key != ~0ull;
+            const int slot = hit ? (int)(uint32_t)key : -1;
+            const int row = ag[i].newrow;
+            uint8_t dep = hit ? (uint8_t)(int)__uint_as_float((uint32_t)(key >> 32)) : (uint8_t)255;
+            const int8_t sem = hit ? (int8_t)spec[slot] : (int8_t)-1;
+            if (ray == 0) dep = (uint8_t)(uint32_t)row;          /* "sanity" overwrite (U9) */
+            to.depth[(size_t)row * kSensor + ray] = dep;
+            to.semantic[(size_t)row * kSensor + ray] = sem;
+            if (ray == kFinderRay) d.target[base + i] = (int16_t)slot;
+        }
+        __syncthreads();
     }
 }
 
@@ -703,14 +767,16 @@ void launch_init(const SimDev &d, cudaStream_t s)
     init_kernel<<<d.numWorlds, threads, 0, s>>>(d);
 }
 
-void launch_step(const SimDev &d, int cur, cudaStream_t s)
+void launch_step(const SimDev &d, int cur, uint32_t threads, cudaStream_t s)
 {
-    step_kernel<<<d.numWorlds, d.cap, step_smem_bytes(d.cap), s>>>(d, cur);
+    /* threads: a multiple of 32 that covers every live slot and the respawn draws; cap always does */
+    if (threads == 0 || threads > d.cap) threads = d.cap;
+    step_kernel<<<d.numWorlds, threads, step_smem_bytes(d.cap), s>>>(d, cur);
 }
 
 void launch_scan(const SimDev &d, int cur, int count_step, cudaStream_t s)
 {
-    scan_kernel<<<1, kScanThreads, 0, s>>>(d, cur, count_step);
+    scan_kernel<<<(d.numWorlds + kScanTile - 1) / kScanTile, kScanTile, 0, s>>>(d, cur, count_step);
 }
 
 void launch_export(const SimDev &d, int cur, int with_sensors, cudaStream_t s)
