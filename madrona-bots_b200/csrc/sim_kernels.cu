@@ -523,125 +523,184 @@ __global__ void __launch_bounds__(kScanTile) scan_kernel(SimDev d, int cur, int 
 }
 
 /* ------------------------------------------------------------------------- */
-/* export_kernel                                                               */
+/* export_kernel: one WARP per world, kExportWarps independent worlds per CTA.  */
+/* No block barriers: every phase of a world is synchronised with __syncwarp,   */
+/* so warps drift apart and hide each other's memory latency.                   */
 
-constexpr int kExportThreads = 128;
+constexpr int kExportWarps = 4;
+constexpr int kSenseTile = 4;        /* observers per sensor pass of a warp */
 
-struct ExportAgent { float x, y; int newrow, oldrow; };
-
-constexpr int kSenseTile = 32;   /* observers per sensor pass: 32 x 32 rays x (16 + 8) B of shared memory */
-
-size_t export_smem_bytes(uint32_t cap)
+/* per-warp shared memory: agent arrays sized for `slots` agents + one sensor tile */
+struct ExportLayout {
+    uint32_t pos, newrow, oldrow, theta, spec, dir, qa, best, total;
+};
+__host__ __device__ inline ExportLayout export_layout(uint32_t slots)
 {
-    return (size_t)kSenseTile * kSensor * (sizeof(float4) + sizeof(unsigned long long)) +
-           (size_t)cap * (sizeof(ExportAgent) + 4 /*theta*/ + 1 /*species*/) + 16;
+    ExportLayout L;
+    uint32_t o = 0;
+    L.best = o; o += kSenseTile * kSensor * 8;          /* u64, 8-byte aligned first */
+    L.dir = o; o += kSenseTile * kSensor * 8;           /* float2 */
+    L.pos = o; o += slots * 8;                          /* float2 */
+    L.qa = o; o += kSenseTile * kSensor * 4;
+    L.newrow = o; o += slots * 4;
+    L.oldrow = o; o += slots * 4;
+    L.theta = o; o += slots * 4;
+    L.spec = o; o += (slots + 15u) & ~15u;
+    L.total = (o + 15u) & ~15u;
+    return L;
 }
 
-/* Copy one column of every agent of the world from its old row to its new row.
- * VEC = bytes per lane access, PARTS = row bytes / VEC. A created-this-step record
- * (old row < 0) is zero-filled (DEVIATIONS.md D3). */
-template <typename V, int PARTS>
-__device__ __forceinline__ void carry_column(void *dst, const void *src, const ExportAgent *ag, int n)
+size_t export_smem_bytes(uint32_t slots) { return (size_t)export_layout(slots).total * kExportWarps; }
+
+/* Copy one column of every agent of the world from its old row to its new row; lanes run over
+ * (agent, part) so that consecutive lanes touch consecutive bytes. V = bytes per lane access,
+ * PARTS = row bytes / sizeof(V). All loads of a batch are issued before its stores. A record
+ * created this step (old row < 0) is zero-filled (DEVIATIONS.md D3). */
+template <typename V, int PARTS, int UNROLL>
+__device__ __forceinline__ void carry_column(void *dst, const void *src, const int *newrow, const int *oldrow,
+                                             int n, int lane)
 {
     const int tasks = n * PARTS;
     V *dp = reinterpret_cast<V *>(dst);
     const V *sp = reinterpret_cast<const V *>(src);
-    for (int t = threadIdx.x; t < tasks; t += kExportThreads) {
-        const int a = t / PARTS, p = t - a * PARTS;
-        const int o = ag[a].oldrow;
-        V v = V();
-        if (o >= 0) v = sp[(size_t)o * PARTS + p];
-        dp[(size_t)ag[a].newrow * PARTS + p] = v;
+    for (int t0 = lane; t0 < tasks; t0 += 32 * UNROLL) {
+        V v[UNROLL];
+        size_t di[UNROLL];
+#pragma unroll
+        for (int u = 0; u < UNROLL; ++u) {
+            const int t = t0 + 32 * u;
+            v[u] = V();
+            di[u] = 0;
+            if (t < tasks) {
+                const int a = t / PARTS, p = t - a * PARTS;
+                const int o = oldrow[a];
+                di[u] = (size_t)newrow[a] * PARTS + p;
+                if (o >= 0) v[u] = sp[(size_t)o * PARTS + p];
+            }
+        }
+#pragma unroll
+        for (int u = 0; u < UNROLL; ++u)
+            if (t0 + 32 * u < tasks) dp[di[u]] = v[u];
     }
 }
 
-__global__ void __launch_bounds__(kExportThreads) export_kernel(SimDev d, int cur, int with_sensors)
+__global__ void __launch_bounds__(kExportWarps * 32) export_kernel(SimDev d, int cur, int with_sensors, uint32_t slots)
 {
     extern __shared__ __align__(16) unsigned char smem_raw[];
-    const uint32_t cap = d.cap;
-    float4 *rays = reinterpret_cast<float4 *>(smem_raw);
-    unsigned long long *best = reinterpret_cast<unsigned long long *>(rays + kSenseTile * kSensor);
-    ExportAgent *ag = reinterpret_cast<ExportAgent *>(best + kSenseTile * kSensor);
-    float *theta = reinterpret_cast<float *>(ag + cap);
-    uint8_t *spec = reinterpret_cast<uint8_t *>(theta + cap);
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const uint32_t w = blockIdx.x * kExportWarps + warp;
+    if (w >= d.numWorlds) return;                       /* whole warp: no block-level barrier below */
+    const ExportLayout L = export_layout(slots);
+    unsigned char *my = smem_raw + (size_t)L.total * warp;
+    unsigned long long *best = reinterpret_cast<unsigned long long *>(my + L.best);
+    float2 *dir = reinterpret_cast<float2 *>(my + L.dir);
+    float2 *pos = reinterpret_cast<float2 *>(my + L.pos);
+    float *qa = reinterpret_cast<float *>(my + L.qa);
+    int *newrow = reinterpret_cast<int *>(my + L.newrow);
+    int *oldrow = reinterpret_cast<int *>(my + L.oldrow);
+    float *theta = reinterpret_cast<float *>(my + L.theta);
+    uint8_t *spec = my + L.spec;
 
-    const uint32_t w = blockIdx.x;
-    const int tid = threadIdx.x;
-    const size_t base = (size_t)w * cap;
+    const size_t base = (size_t)w * d.cap;
     const ObsSet &from = d.obs[cur];
     const ObsSet &to = d.obs[cur ^ 1];
     const int n = d.worldCount[w];
     const int4 rb = d.rowBase[cur ^ 1][w];
     const int off = d.worldOffset[w];
     const float4 srew = d.speciesReward[w];
+    const unsigned lt = (1u << lane) - 1u;
 
-    /* stage */
-    for (int s = tid; s < n; s += kExportThreads) {
-        const float4 p = d.pose[base + s];
-        const float4 sc = d.scratch[base + s];
-        ag[s].x = p.x; ag[s].y = p.y;
-        ag[s].oldrow = __float_as_int(sc.x);
-        theta[s] = view_yaw(Rot{p.z, p.w});
-        spec[s] = d.species[base + s];
+    /* ---- per agent (one lane each): new row, observation exports, small carried columns ---- */
+    int seen[4] = {0, 0, 0, 0};                         /* agents of each species in lower passes */
+    for (int s0 = 0; s0 < n; s0 += 32) {
+        const int s = s0 + lane;
+        const bool on = s < n;
+        float4 p = make_float4(0.f, 0.f, 1.f, 0.f), sc = make_float4(0.f, 0.f, 0.f, 0.f);
+        int sp = 0, hp = 0;
+        if (on) {
+            p = d.pose[base + s];
+            sc = d.scratch[base + s];
+            sp = d.species[base + s];
+            hp = d.health[base + s];
+        }
+        /* new row = first row of (world, species) + rank among lower slots of the species */
+        int rank = 0;
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            const unsigned bsp = __ballot_sync(FULL, on && sp == k + 1);
+            if (sp == k + 1) rank = seen[k] + __popc(bsp & lt);
+            seen[k] += __popc(bsp);
+        }
+        if (on) {
+            const int row = comp(rb, sp - 1) + rank;
+            const int old = __float_as_int(sc.x);
+            /* carried small columns: issue the loads first */
+            int4 pst = make_int4(0, 0, 0, 0);
+            float2 ppos = make_float2(0.f, 0.f), psur = make_float2(0.f, 0.f);
+            float prew = 0.f, phl = 0.f;
+            if (old >= 0) {
+                pst = reinterpret_cast<const int4 *>(from.prev_stats)[old];
+                ppos = reinterpret_cast<const float2 *>(from.prev_position)[old];
+                psur = reinterpret_cast<const float2 *>(from.prev_surrounding)[old];
+                prew = from.prev_reward[old];
+                phl = from.prev_health[old];
+            }
+            pos[s] = make_float2(p.x, p.y);
+            newrow[s] = row;
+            oldrow[s] = old;
+            theta[s] = view_yaw(Rot{p.z, p.w});
+            spec[s] = (uint8_t)sp;
+            /* updateObservations (:687-717), rewardSystem (:943-956), SensorOutputIndex (:783-784) */
+            const uint32_t st = (uint32_t)__float_as_int(sc.w);
+            reinterpret_cast<float2 *>(to.position)[row] = make_float2(p.x, p.y);
+            to.health[row] = (float)hp;
+            reinterpret_cast<float2 *>(to.surrounding)[row] = make_float2(sc.y, sc.z);
+            reinterpret_cast<int4 *>(to.stats)[row] = make_int4(st & 1u, (st >> 1) & 1u, (st >> 2) & 1u, (st >> 3) & 1u);
+            const float sterm = sp == 1 ? srew.x : sp == 2 ? srew.y : sp == 3 ? srew.z : srew.w;
+            to.reward[row] = with_sensors ? agent_reward(sterm, hp, (st & 4u) != 0, (st & 8u) != 0, (st & 2u) != 0) : 0.f;
+            d.sensorIndex[off + s] = row;
+            if (!with_sensors) d.target[base + s] = (int16_t)-1;
+            reinterpret_cast<int4 *>(to.prev_stats)[row] = pst;
+            reinterpret_cast<float2 *>(to.prev_position)[row] = ppos;
+            reinterpret_cast<float2 *>(to.prev_surrounding)[row] = psur;
+            to.prev_reward[row] = prew;
+            to.prev_health[row] = phl;
+        }
     }
-    __syncthreads();
-    /* new row = first row of (world, species) + rank among lower slots of the species */
-    for (int s = tid; s < n; s += kExportThreads) {
-        const int sp = spec[s];
-        int r = 0;
-        for (int j = 0; j < s; ++j) r += (spec[j] == sp);
-        const int row = comp(rb, sp - 1) + r;
-        ag[s].newrow = row;
+    __syncwarp();
 
-        /* updateObservations (:687-717), rewardSystem (:943-956), SensorOutputIndex (:783-784) */
-        const float4 sc = d.scratch[base + s];
-        const int hp = d.health[base + s];
-        const uint32_t st = (uint32_t)__float_as_int(sc.w);
-        reinterpret_cast<float2 *>(to.position)[row] = make_float2(ag[s].x, ag[s].y);
-        to.health[row] = (float)hp;
-        reinterpret_cast<float2 *>(to.surrounding)[row] = make_float2(sc.y, sc.z);
-        reinterpret_cast<int4 *>(to.stats)[row] = make_int4(st & 1u, (st >> 1) & 1u, (st >> 2) & 1u, (st >> 3) & 1u);
-        const float sterm = sp == 1 ? srew.x : sp == 2 ? srew.y : sp == 3 ? srew.z : srew.w;
-        to.reward[row] = with_sensors ? agent_reward(sterm, hp, (st & 4u) != 0, (st & 8u) != 0, (st & 2u) != 0) : 0.f;
-        d.sensorIndex[off + s] = row;
-        if (!with_sensors) d.target[base + s] = (int16_t)-1;
-    }
-    __syncthreads();
-
-    /* the sort: every column of the observation record follows its agent */
-    carry_column<int2, 3>(to.action, from.action, ag, n);
-    carry_column<int2, 3>(to.prev_action, from.prev_action, ag, n);
-    carry_column<float4, 4>(to.hidden, from.hidden, ag, n);
-    carry_column<float4, 4>(to.prev_hidden, from.prev_hidden, ag, n);
-    carry_column<int4, 1>(to.prev_stats, from.prev_stats, ag, n);
-    carry_column<float2, 1>(to.prev_position, from.prev_position, ag, n);
-    carry_column<float2, 1>(to.prev_surrounding, from.prev_surrounding, ag, n);
-    carry_column<float, 1>(to.prev_reward, from.prev_reward, ag, n);
-    carry_column<float, 1>(to.prev_health, from.prev_health, ag, n);
+    /* ---- the sort: the wide columns of the observation record follow their agent ---- */
+    carry_column<float4, 4, 3>(to.hidden, from.hidden, newrow, oldrow, n, lane);
+    carry_column<float4, 4, 3>(to.prev_hidden, from.prev_hidden, newrow, oldrow, n, lane);
+    carry_column<int2, 3, 4>(to.action, from.action, newrow, oldrow, n, lane);
+    carry_column<int2, 3, 4>(to.prev_action, from.prev_action, newrow, oldrow, n, lane);
     /* updateSensorOutputIdx (:774-780): last frame's sensor rows become the prev rows */
-    carry_column<int4, 2>(to.prev_semantic, from.semantic, ag, n);
-    carry_column<int4, 2>(to.prev_depth, from.depth, ag, n);
+    carry_column<int4, 2, 3>(to.prev_semantic, from.semantic, newrow, oldrow, n, lane);
+    carry_column<int4, 2, 3>(to.prev_depth, from.depth, newrow, oldrow, n, lane);
 
     if (!with_sensors) return;
 
-    /* Sensor (M/src/mw/device/bvh_raycast.cpp:193-305), agents in tiles of kSenseTile:
-     *  1. one thread per (agent, ray): ray direction + quadratic constants -> shared memory
-     *  2. one thread per (agent, target) pair: conservative candidate rays (pair_candidates),
+    /* ---- sensor (M/src/mw/device/bvh_raycast.cpp:193-305), observers in tiles of kSenseTile:
+     *  1. one lane per (observer, ray): ray direction and quadratic coefficient -> shared memory
+     *  2. one lane per (observer, target) pair: conservative candidate rays (pair_candidates),
      *     exact ray/sphere test on those only, nearest accepted hit kept with a 64-bit
      *     shared-memory atomicMin on (t bits << 32 | target slot)  -- ties go to the lowest slot
-     *  3. one thread per (agent, ray): decode, write depth / semantic bytes and the finder hit */
+     *  3. one lane per (observer, 4 rays): decode, write 4 depth + 4 semantic bytes, finder hit */
+    const uint32_t magic = 0xffffffffu / (uint32_t)n + 1u;   /* p / n == umulhi(p, magic) for p * n < 2^32 */
     for (int tile0 = 0; tile0 < n; tile0 += kSenseTile) {
         const int m = min(kSenseTile, n - tile0);
-        for (int idx = tid; idx < m * kSensor; idx += kExportThreads) {
+        for (int idx = lane; idx < m * kSensor; idx += 32) {
             const Ray r = make_ray(theta[tile0 + (idx >> 5)], idx & 31);
-            rays[idx] = make_float4(r.dx, r.dy, r.a4, r.a2);
+            dir[idx] = make_float2(r.dx, r.dy);
+            qa[idx] = r.a;
             best[idx] = ~0ull;
         }
-        __syncthreads();
+        __syncwarp();
         const int pairs = m * n;
-        for (int p = tid; p < pairs; p += kExportThreads) {
-            const int il = p / n, j = p - il * n, i = tile0 + il;
-            const float ocx = ag[i].x - ag[j].x, ocy = ag[i].y - ag[j].y;
+        for (int p = lane; p < pairs; p += 32) {
+            const int il = (int)__umulhi((uint32_t)p, magic), j = p - il * n, i = tile0 + il;
+            const float2 pi = pos[i], pj = pos[j];
+            const float ocx = pi.x - pj.x, ocy = pi.y - pj.y;
             RaySpan sp;
             if (!pair_candidates(ocx, ocy, theta[i], sp)) continue;
             const float c = (ocx * ocx + ocy * ocy) - 1.f;
@@ -649,11 +708,12 @@ __global__ void __launch_bounds__(kExportThreads) export_kernel(SimDev d, int cu
             int r = sp.flo <= sp.fhi ? sp.flo : kFwdRays + sp.blo;
             const int rend = sp.blo <= sp.bhi ? kFwdRays + sp.bhi : sp.fhi;
             while (r <= rend) {
-                const float4 q = rays[il * kSensor + r];
+                const float2 q = dir[il * kSensor + r];
+                const float a = qa[il * kSensor + r];
                 const float bq = 2.0f * (ocx * q.x + ocy * q.y);
-                const float disc = bq * bq - q.z * c;
+                const float disc = bq * bq - (4.f * a) * c;
                 if (disc >= 0.f) {
-                    const float t = (-bq - sqrtf(disc)) / q.w;
+                    const float t = (-bq - sqrtf(disc)) / (2.0f * a);
                     if (t > kNearSphere)
                         atomicMin(&best[il * kSensor + r],
                                   ((unsigned long long)__float_as_uint(t) << 32) | (unsigned long long)(uint32_t)j);
@@ -661,21 +721,27 @@ __global__ void __launch_bounds__(kExportThreads) export_kernel(SimDev d, int cu
                 r = (r == sp.fhi && r < kFwdRays) ? kFwdRays + sp.blo : r + 1;
             }
         }
-        __syncthreads();
-        for (int idx = tid; idx < m * kSensor; idx += kExportThreads) {
-            const int i = tile0 + (idx >> 5), ray = idx & 31;
-            const unsigned long long key = best[idx];
-            const bool hit = key != ~0ull;
-            const int slot = hit ? (int)(uint32_t)key : -1;
-            const int row = ag[i].newrow;
-            uint8_t dep = hit ? (uint8_t)(int)__uint_as_float((uint32_t)(key >> 32)) : (uint8_t)255;
-            const int8_t sem = hit ? (int8_t)spec[slot] : (int8_t)-1;
-            if (ray == 0) dep = (uint8_t)(uint32_t)row;          /* "sanity" overwrite (U9) */
-            to.depth[(size_t)row * kSensor + ray] = dep;
-            to.semantic[(size_t)row * kSensor + ray] = sem;
-            if (ray == kFinderRay) d.target[base + i] = (int16_t)slot;
+        __syncwarp();
+        for (int idx = lane; idx < m * 8; idx += 32) {
+            const int il = idx >> 3, quad = idx & 7, i = tile0 + il;
+            const int row = newrow[i];
+            uint32_t dep = 0, sem = 0;
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+                const unsigned long long key = best[il * kSensor + quad * 4 + k];
+                const bool hit = key != ~0ull;
+                const int slot = hit ? (int)(uint32_t)key : -1;
+                uint32_t dv = hit ? (uint32_t)(uint8_t)(int)__uint_as_float((uint32_t)(key >> 32)) : 255u;
+                const uint32_t sv = hit ? (uint32_t)spec[slot] : 0xffu;
+                if (quad == 0 && k == 0) dv = (uint32_t)row & 0xffu;      /* "sanity" overwrite (U9) */
+                if (quad == kFinderRay / 4 && k == kFinderRay % 4) d.target[base + i] = (int16_t)slot;
+                dep |= dv << (8 * k);
+                sem |= sv << (8 * k);
+            }
+            reinterpret_cast<uint32_t *>(to.depth)[(size_t)row * 8 + quad] = dep;
+            reinterpret_cast<uint32_t *>(to.semantic)[(size_t)row * 8 + quad] = sem;
         }
-        __syncthreads();
+        __syncwarp();
     }
 }
 
@@ -779,9 +845,14 @@ void launch_scan(const SimDev &d, int cur, int count_step, cudaStream_t s)
     scan_kernel<<<(d.numWorlds + kScanTile - 1) / kScanTile, kScanTile, 0, s>>>(d, cur, count_step);
 }
 
-void launch_export(const SimDev &d, int cur, int with_sensors, cudaStream_t s)
+void launch_export(const SimDev &d, int cur, int with_sensors, uint32_t slots, cudaStream_t s)
 {
-    export_kernel<<<d.numWorlds, kExportThreads, export_smem_bytes(d.cap), s>>>(d, cur, with_sensors);
+    /* slots: per-warp staging capacity, >= the largest world; the capacity always is */
+    if (slots == 0 || slots > d.cap) slots = d.cap;
+    const size_t smem = export_smem_bytes(slots);
+    if (smem > 48 * 1024)
+        cudaFuncSetAttribute(export_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    export_kernel<<<(d.numWorlds + kExportWarps - 1) / kExportWarps, kExportWarps * 32, smem, s>>>(d, cur, with_sensors, slots);
 }
 
 void launch_shift(const SimDev &d, int cur, uint32_t rows_upper, cudaStream_t s)
