@@ -528,20 +528,21 @@ __global__ void __launch_bounds__(kScanTile) scan_kernel(SimDev d, int cur, int 
 /* so warps drift apart and hide each other's memory latency.                   */
 
 constexpr int kExportWarps = 4;
-constexpr int kSenseTile = 4;        /* observers per sensor pass of a warp */
+constexpr int kSenseTile = 8;        /* observers per sensor pass of a warp */
+constexpr int kQueue = 64;           /* pending exact tests of a warp (< 32 before a push round, + 32) */
 
 /* per-warp shared memory: agent arrays sized for `slots` agents + one sensor tile */
 struct ExportLayout {
-    uint32_t pos, newrow, oldrow, theta, spec, dir, qa, best, total;
+    uint32_t best, pos, head, queue, newrow, oldrow, theta, spec, total;
 };
 __host__ __device__ inline ExportLayout export_layout(uint32_t slots)
 {
     ExportLayout L;
     uint32_t o = 0;
     L.best = o; o += kSenseTile * kSensor * 8;          /* u64, 8-byte aligned first */
-    L.dir = o; o += kSenseTile * kSensor * 8;           /* float2 */
     L.pos = o; o += slots * 8;                          /* float2 */
-    L.qa = o; o += kSenseTile * kSensor * 4;
+    L.head = o; o += slots * 8;                         /* float2 unit heading (cull only) */
+    L.queue = o; o += kQueue * 4;
     L.newrow = o; o += slots * 4;
     L.oldrow = o; o += slots * 4;
     L.theta = o; o += slots * 4;
@@ -593,9 +594,9 @@ __global__ void __launch_bounds__(kExportWarps * 32) export_kernel(SimDev d, int
     const ExportLayout L = export_layout(slots);
     unsigned char *my = smem_raw + (size_t)L.total * warp;
     unsigned long long *best = reinterpret_cast<unsigned long long *>(my + L.best);
-    float2 *dir = reinterpret_cast<float2 *>(my + L.dir);
     float2 *pos = reinterpret_cast<float2 *>(my + L.pos);
-    float *qa = reinterpret_cast<float *>(my + L.qa);
+    float2 *head = reinterpret_cast<float2 *>(my + L.head);
+    uint32_t *queue = reinterpret_cast<uint32_t *>(my + L.queue);
     int *newrow = reinterpret_cast<int *>(my + L.newrow);
     int *oldrow = reinterpret_cast<int *>(my + L.oldrow);
     float *theta = reinterpret_cast<float *>(my + L.theta);
@@ -649,6 +650,8 @@ __global__ void __launch_bounds__(kExportWarps * 32) export_kernel(SimDev d, int
             newrow[s] = row;
             oldrow[s] = old;
             theta[s] = view_yaw(Rot{p.z, p.w});
+            const Dir hd = cull_heading(Rot{p.z, p.w});
+            head[s] = make_float2(hd.x, hd.y);
             spec[s] = (uint8_t)sp;
             /* updateObservations (:687-717), rewardSystem (:943-956), SensorOutputIndex (:783-784) */
             const uint32_t st = (uint32_t)__float_as_int(sc.w);
@@ -681,47 +684,72 @@ __global__ void __launch_bounds__(kExportWarps * 32) export_kernel(SimDev d, int
     if (!with_sensors) return;
 
     /* ---- sensor (M/src/mw/device/bvh_raycast.cpp:193-305), observers in tiles of kSenseTile:
-     *  1. one lane per (observer, ray): ray direction and quadratic coefficient -> shared memory
-     *  2. one lane per (observer, target) pair: conservative candidate rays (pair_candidates),
-     *     exact ray/sphere test on those only, nearest accepted hit kept with a 64-bit
-     *     shared-memory atomicMin on (t bits << 32 | target slot)  -- ties go to the lowest slot
+     *  1. one lane per (observer, target) pair: conservative candidate rays (pair_candidates).
+     *     Candidates are rare (~0.27 per pair) and ragged, so they are not tested in place:
+     *     each one is pushed as (observer, target, ray) onto a per-warp queue, and whenever 32
+     *     are pending the warp runs the exact test on 32 of them at full lane occupancy.
+     *  2. exact test (make_ray + ray/sphere, the oracle's arithmetic): nearest accepted hit kept
+     *     with a 64-bit shared-memory atomicMin on (t bits << 32 | target slot) -- ties go to
+     *     the lowest slot, and the order in which candidates are tested does not matter.
      *  3. one lane per (observer, 4 rays): decode, write 4 depth + 4 semantic bytes, finder hit */
     const uint32_t magic = 0xffffffffu / (uint32_t)n + 1u;   /* p / n == umulhi(p, magic) for p * n < 2^32 */
     for (int tile0 = 0; tile0 < n; tile0 += kSenseTile) {
         const int m = min(kSenseTile, n - tile0);
-        for (int idx = lane; idx < m * kSensor; idx += 32) {
-            const Ray r = make_ray(theta[tile0 + (idx >> 5)], idx & 31);
-            dir[idx] = make_float2(r.dx, r.dy);
-            qa[idx] = r.a;
-            best[idx] = ~0ull;
-        }
+        for (int idx = lane; idx < m * kSensor; idx += 32) best[idx] = ~0ull;
         __syncwarp();
+
+        auto run_tests = [&](int first, int count) {
+            if (lane < count) {
+                const uint32_t e = queue[first + lane];
+                const int r = (int)(e & 31u), j = (int)((e >> 5) & 1023u), il = (int)(e >> 15);
+                const int i = tile0 + il;
+                const float2 pi = pos[i], pj = pos[j];
+                const Ray ray = make_ray(theta[i], r);
+                float t;
+                if (ray_sphere(ray, pi.x - pj.x, pi.y - pj.y, t) && t > kNearSphere)
+                    atomicMin(&best[il * kSensor + r],
+                              ((unsigned long long)__float_as_uint(t) << 32) | (unsigned long long)(uint32_t)j);
+            }
+        };
+
+        int qn = 0;                                     /* warp-uniform */
         const int pairs = m * n;
-        for (int p = lane; p < pairs; p += 32) {
-            const int il = (int)__umulhi((uint32_t)p, magic), j = p - il * n, i = tile0 + il;
-            const float2 pi = pos[i], pj = pos[j];
-            const float ocx = pi.x - pj.x, ocy = pi.y - pj.y;
-            RaySpan sp;
-            if (!pair_candidates(ocx, ocy, theta[i], sp)) continue;
-            const float c = (ocx * ocx + ocy * ocy) - 1.f;
-            /* one loop over both fans: forward rays flo..fhi, then backward rays 24+blo..24+bhi */
-            int r = sp.flo <= sp.fhi ? sp.flo : kFwdRays + sp.blo;
-            const int rend = sp.blo <= sp.bhi ? kFwdRays + sp.bhi : sp.fhi;
-            while (r <= rend) {
-                const float2 q = dir[il * kSensor + r];
-                const float a = qa[il * kSensor + r];
-                const float bq = 2.0f * (ocx * q.x + ocy * q.y);
-                const float disc = bq * bq - (4.f * a) * c;
-                if (disc >= 0.f) {
-                    const float t = (-bq - sqrtf(disc)) / (2.0f * a);
-                    if (t > kNearSphere)
-                        atomicMin(&best[il * kSensor + r],
-                                  ((unsigned long long)__float_as_uint(t) << 32) | (unsigned long long)(uint32_t)j);
+        for (int p0 = 0; p0 < pairs; p0 += 32) {
+            const int p = p0 + lane;
+            int cf = 0, cb = 0, il = 0, j = 0;
+            RaySpan sp = {0, -1, 0, -1};
+            if (p < pairs) {
+                il = (int)__umulhi((uint32_t)p, magic);
+                j = p - il * n;
+                const int i = tile0 + il;
+                const float2 pi = pos[i], pj = pos[j], hd = head[i];
+                if (pair_candidates(pi.x - pj.x, pi.y - pj.y, Dir{hd.x, hd.y}, sp)) {
+                    cf = max(0, sp.fhi - sp.flo + 1);
+                    cb = max(0, sp.bhi - sp.blo + 1);
                 }
-                r = (r == sp.fhi && r < kFwdRays) ? kFwdRays + sp.blo : r + 1;
+            }
+            const int c = cf + cb;
+            const uint32_t tag = ((uint32_t)il << 15) | ((uint32_t)j << 5);
+            for (int k = 0;; ++k) {
+                const bool has = k < c;
+                const unsigned mk = __ballot_sync(FULL, has);
+                if (!mk) break;
+                if (has) {
+                    const int r = k < cf ? sp.flo + k : kFwdRays + sp.blo + (k - cf);
+                    queue[qn + __popc(mk & lt)] = tag | (uint32_t)r;
+                }
+                qn += __popc(mk);
+                __syncwarp();
+                if (qn >= 32) {
+                    run_tests(qn - 32, 32);
+                    qn -= 32;
+                    __syncwarp();
+                }
             }
         }
+        if (qn > 0) run_tests(0, qn);
         __syncwarp();
+
         for (int idx = lane; idx < m * 8; idx += 32) {
             const int il = idx >> 3, quad = idx & 7, i = tile0 + il;
             const int row = newrow[i];

@@ -278,7 +278,7 @@ MBP_HD bool ray_sphere(const Ray &r, float ocx, float ocy, float &t)
 struct RaySpan { int flo, fhi, blo, bhi; };
 
 constexpr float kCullMinDist2 = 1.2f;        /* D < 1.095: t <= D < 1.1, nothing can be accepted */
-constexpr float kCullAngleMargin = 3e-4f;    /* rad */
+constexpr float kCullAngleMargin = 5e-4f;    /* rad; covers the 1e-5 rad of cull_atan2 and the approximate division */
 
 MBP_HD float inv_sqrt_upper(float v)
 {
@@ -289,25 +289,78 @@ MBP_HD float inv_sqrt_upper(float v)
 #endif
 }
 
-MBP_HD bool pair_candidates(float ocx, float ocy, float theta, RaySpan &sp)
+/* Unit heading of an observer for the cull (direction of rot * x-hat; the exact yaw the rays
+ * use is atan2 of the same vector, so the two agree to ~1e-6 rad). */
+MBP_HD Dir cull_heading(Rot r)
+{
+    const Dir f = rot_forward(r);
+#if defined(__CUDA_ARCH__)
+    const float inv = rsqrtf(f.x * f.x + f.y * f.y);
+#else
+    const float inv = 1.f / sqrtf(f.x * f.x + f.y * f.y);
+#endif
+    return Dir{f.x * inv, f.y * inv};
+}
+
+/* atan2 to ~1e-5 rad (Abramowitz & Stegun 4.4.49 on the reduced octant); cull use only. */
+MBP_HD float cull_atan2(float y, float x)
+{
+    const float ax = fabsf(x), ay = fabsf(y);
+    const float mx = fmaxf(ax, ay), mn = fminf(ax, ay);
+#if defined(__CUDA_ARCH__)
+    const float q = __fdividef(mn, mx);
+#else
+    const float q = mn / mx;
+#endif
+    const float s = q * q;
+    float r = mb_fmaf(0.0208351f, s, -0.0851330f);
+    r = mb_fmaf(r, s, 0.1801410f);
+    r = mb_fmaf(r, s, -0.3302995f);
+    r = mb_fmaf(r, s, 0.9998660f);
+    r = r * q;
+    if (ay > ax) r = 0x1.921fb6p+0f - r;
+    if (x < 0.f) r = 0x1.921fb6p+1f - r;
+    return y < 0.f ? -r : r;
+}
+
+MBP_HD int cull_ceil(float v)
+{
+#if defined(__CUDA_ARCH__)
+    return __float2int_ru(v);
+#else
+    return (int)ceilf(v);
+#endif
+}
+MBP_HD int cull_floor(float v)
+{
+#if defined(__CUDA_ARCH__)
+    return __float2int_rd(v);
+#else
+    return (int)floorf(v);
+#endif
+}
+
+/* oc = observer - target, h = unit heading of the observer */
+MBP_HD bool pair_candidates(float ocx, float ocy, Dir h, RaySpan &sp)
 {
     const float d2 = ocx * ocx + ocy * ocy;
     if (!(d2 >= kCullMinDist2)) return false;
     const float x = inv_sqrt_upper(d2);                          /* >= 1/D, <= 0.914 */
     const float half = x * (1.f + 0.32f * x * x) + kCullAngleMargin;   /* >= asin(1.0005/D) on (0, 0.914] */
-    float rho = mb_atan2f(-ocy, -ocx) - theta;                    /* direction to the target, relative to the heading */
-    if (rho >= kPi) rho -= 2.f * kPi;
-    if (rho < -kPi) rho += 2.f * kPi;
+    /* direction to the target (-oc) in the heading frame: along, left */
+    const float al = -(ocx * h.x + ocy * h.y);
+    const float lf = ocx * h.y - ocy * h.x;
+    const float rho = cull_atan2(lf, al);                         /* in [-pi, pi] */
     const float inv_df = ((float)kFwdRays - 1.f) / (kPi * 0.5f);
     const float inv_db = ((float)(kSensor - kFwdRays) - 1.f) / (kPi * 0.5f);
     const float f0 = rho + kPi * 0.25f;
-    sp.flo = (int)ceilf((f0 - half) * inv_df);
-    sp.fhi = (int)floorf((f0 + half) * inv_df);
+    sp.flo = cull_ceil((f0 - half) * inv_df);
+    sp.fhi = cull_floor((f0 + half) * inv_df);
     if (sp.flo < 0) sp.flo = 0;
     if (sp.fhi > kFwdRays - 1) sp.fhi = kFwdRays - 1;
     const float rb = (rho < 0.f ? rho + kPi : rho - kPi) + kPi * 0.25f;
-    sp.blo = (int)ceilf((rb - half) * inv_db);
-    sp.bhi = (int)floorf((rb + half) * inv_db);
+    sp.blo = cull_ceil((rb - half) * inv_db);
+    sp.bhi = cull_floor((rb + half) * inv_db);
     if (sp.blo < 0) sp.blo = 0;
     if (sp.bhi > kSensor - kFwdRays - 1) sp.bhi = kSensor - kFwdRays - 1;
     return sp.flo <= sp.fhi || sp.blo <= sp.bhi;

@@ -57,15 +57,15 @@ static void sense_brute(int n, const float *x, const float *y, int self, float t
 }
 
 /* culled sensor: the algorithm of export_kernel, sequentially */
-static void sense_culled(int n, const float *x, const float *y, int self, float theta, float *t_out, int *slot_out,
-                         long long *tests)
+static void sense_culled(int n, const float *x, const float *y, int self, float theta, Dir h, float *t_out,
+                         int *slot_out, long long *tests)
 {
     Ray rays[kSensor];
     for (int r = 0; r < kSensor; ++r) { rays[r] = make_ray(theta, r); t_out[r] = 0.f; slot_out[r] = -1; }
     for (int j = 0; j < n; ++j) {
         const float ocx = x[self] - x[j], ocy = y[self] - y[j];
         RaySpan sp;
-        if (!pair_candidates(ocx, ocy, theta, sp)) continue;
+        if (!pair_candidates(ocx, ocy, h, sp)) continue;
         for (int pass = 0; pass < 2; ++pass) {
             const int lo = pass == 0 ? sp.flo : kFwdRays + sp.blo, hi = pass == 0 ? sp.fhi : kFwdRays + sp.bhi;
             for (int r = lo; r <= hi; ++r) {
@@ -90,7 +90,12 @@ long long shim_cull_trials(uint64_t seed, int trials, int n, int mode, long long
     *exact_tests = 0;
     uint64_t s = seed * 2654435761ull + 12345ull;
     for (int tr = 0; tr < trials; ++tr) {
-        const float theta = (urand(s) * 2.f - 1.f) * kPi;
+        /* heading as the simulator has it: a (w, z) rotation; yaw and cull heading derive from it */
+        const float ang = (urand(s) * 2.f - 1.f) * kPi * 0.5f;
+        const float nrm = 1.f + (urand(s) - 0.5f) * 2e-3f;      /* slightly denormalised, as after many turns */
+        const Rot rot{cosf(ang) * nrm, sinf(ang) * nrm};
+        const float theta = view_yaw(rot);
+        const Dir h = cull_heading(rot);
         const float span = mode == 1 ? 6.f : 1.f;
         for (int j = 0; j < n; ++j) {
             x[j] = mode == 1 ? 60.f + urand(s) * span : urand(s) * 127.f;
@@ -112,7 +117,7 @@ long long shim_cull_trials(uint64_t seed, int trials, int n, int mode, long long
         const int observers = mode == 2 ? 1 : n;
         for (int i = 0; i < observers; ++i) {
             sense_brute(n, x.data(), y.data(), i, theta, tb, sb);
-            sense_culled(n, x.data(), y.data(), i, theta, tc, sc, exact_tests);
+            sense_culled(n, x.data(), y.data(), i, theta, h, tc, sc, exact_tests);
             for (int r = 0; r < kSensor; ++r)
                 if (sb[r] != sc[r] || (sb[r] >= 0 && tb[r] != tc[r])) ++bad;
         }
