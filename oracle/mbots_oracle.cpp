@@ -49,7 +49,7 @@ public:
         stop();
         nthreads_ = std::max(1, n);
         quit_ = false;
-        for (int i = 1; i < nthreads_; ++i) workers_.emplace_back([this, i] { loop(i); });
+        for (int i = 1; i < nthreads_; ++i) workers_.emplace_back([this, i, e = epoch_] { loop(i, e); });
     }
     void parallel_for(int64_t n, const std::function<void(int64_t)> &fn)
     {
@@ -70,9 +70,8 @@ private:
         int64_t b = per * t, e = std::min<int64_t>(n_, b + per);
         for (int64_t i = b; i < e; ++i) (*fn_)(i);
     }
-    void loop(int t)
+    void loop(int t, uint64_t seen)   /* seen: the epoch at creation (a resized pool must not replay old work) */
     {
-        uint64_t seen = 0;
         for (;;) {
             {
                 std::unique_lock<std::mutex> lk(m_);
