@@ -529,11 +529,11 @@ __global__ void __launch_bounds__(kScanTile) scan_kernel(SimDev d, int cur, int 
 
 constexpr int kExportWarps = 4;
 constexpr int kSenseTile = 8;        /* observers per sensor pass of a warp */
-constexpr int kQueue = 64;           /* pending exact tests of a warp (< 32 before a push round, + 32) */
+constexpr int kQueue = 64;           /* pending pairs / pending exact tests of a warp: < 32 carried over, + <= 32 pushed */
 
 /* per-warp shared memory: agent arrays sized for `slots` agents + one sensor tile */
 struct ExportLayout {
-    uint32_t best, pos, head, queue, newrow, oldrow, theta, spec, total;
+    uint32_t best, pos, head, queue, pairq, newrow, oldrow, theta, spec, total;
 };
 __host__ __device__ inline ExportLayout export_layout(uint32_t slots)
 {
@@ -543,6 +543,7 @@ __host__ __device__ inline ExportLayout export_layout(uint32_t slots)
     L.pos = o; o += slots * 8;                          /* float2 */
     L.head = o; o += slots * 8;                         /* float2 unit heading (cull only) */
     L.queue = o; o += kQueue * 4;
+    L.pairq = o; o += kQueue * 4;
     L.newrow = o; o += slots * 4;
     L.oldrow = o; o += slots * 4;
     L.theta = o; o += slots * 4;
@@ -597,6 +598,7 @@ __global__ void __launch_bounds__(kExportWarps * 32) export_kernel(SimDev d, int
     float2 *pos = reinterpret_cast<float2 *>(my + L.pos);
     float2 *head = reinterpret_cast<float2 *>(my + L.head);
     uint32_t *queue = reinterpret_cast<uint32_t *>(my + L.queue);
+    uint32_t *pairq = reinterpret_cast<uint32_t *>(my + L.pairq);
     int *newrow = reinterpret_cast<int *>(my + L.newrow);
     int *oldrow = reinterpret_cast<int *>(my + L.oldrow);
     float *theta = reinterpret_cast<float *>(my + L.theta);
@@ -684,79 +686,113 @@ __global__ void __launch_bounds__(kExportWarps * 32) export_kernel(SimDev d, int
     if (!with_sensors) return;
 
     /* ---- sensor (M/src/mw/device/bvh_raycast.cpp:193-305), observers in tiles of kSenseTile:
-     *  1. one lane per (observer, target) pair: conservative candidate rays (pair_candidates).
-     *     Candidates are rare (~0.27 per pair) and ragged, so they are not tested in place:
-     *     each one is pushed as (observer, target, ray) onto a per-warp queue, and whenever 32
-     *     are pending the warp runs the exact test on 32 of them at full lane occupancy.
+     *  1. lanes form a (observer of the tile) x (target) grid -- 8 x 4 for a full tile, narrower for the last
+     *     partial tile -- so a lane keeps its observer in registers and steps through the targets with no
+     *     index arithmetic. Per pair: conservative candidate rays (pair_candidates, ~0.27 per pair).
+     *     Candidates are ragged, so they are not tested in place: a warp scan gives every lane its place in a
+     *     per-warp queue of (observer, target, ray), and whenever 32 are pending the warp runs the exact
+     *     test on 32 of them at full lane occupancy.
      *  2. exact test (make_ray + ray/sphere, the oracle's arithmetic): nearest accepted hit kept
      *     with a 64-bit shared-memory atomicMin on (t bits << 32 | target slot) -- ties go to
      *     the lowest slot, and the order in which candidates are tested does not matter.
      *  3. one lane per (observer, 4 rays): decode, write 4 depth + 4 semantic bytes, finder hit */
-    const uint32_t magic = 0xffffffffu / (uint32_t)n + 1u;   /* p / n == umulhi(p, magic) for p * n < 2^32 */
     for (int tile0 = 0; tile0 < n; tile0 += kSenseTile) {
         const int m = min(kSenseTile, n - tile0);
-        for (int idx = lane; idx < m * kSensor; idx += 32) best[idx] = ~0ull;
+        {
+            ulonglong2 *b2 = reinterpret_cast<ulonglong2 *>(best);
+            for (int idx = lane; idx < m * (kSensor / 2); idx += 32) b2[idx] = make_ulonglong2(~0ull, ~0ull);
+        }
+        const int lg = m > 4 ? 3 : m > 2 ? 2 : m > 1 ? 1 : 0;   /* observers across lanes: 1 << lg >= m */
+        const int il = lane & ((1 << lg) - 1), jl = lane >> lg, tpi = 32 >> lg;
+        const bool on_i = il < m;
+        const float2 pi = pos[tile0 + (on_i ? il : 0)], hd = head[tile0 + (on_i ? il : 0)];
         __syncwarp();
 
-        auto run_tests = [&](int first, int count) {
-            if (lane < count) {
-                const uint32_t e = queue[first + lane];
-                const int r = (int)(e & 31u), j = (int)((e >> 5) & 1023u), il = (int)(e >> 15);
-                const int i = tile0 + il;
-                const float2 pi = pos[i], pj = pos[j];
-                const Ray ray = make_ray(theta[i], r);
-                float t;
-                if (ray_sphere(ray, pi.x - pj.x, pi.y - pj.y, t) && t > kNearSphere)
-                    atomicMin(&best[il * kSensor + r],
-                              ((unsigned long long)__float_as_uint(t) << 32) | (unsigned long long)(uint32_t)j);
-            }
+        auto run_tests = [&](int first) {
+            const uint32_t e = queue[first + lane];
+            const int r = (int)(e & 31u), j = (int)((e >> 5) & 1023u), ql = (int)(e >> 15);
+            const float2 qi = pos[tile0 + ql], qj = pos[j];
+            const Ray ray = make_ray(theta[tile0 + ql], r);
+            float t;
+            if (ray_sphere(ray, qi.x - qj.x, qi.y - qj.y, t) && t > kNearSphere)
+                atomicMin(&best[ql * kSensor + r],
+                          ((unsigned long long)__float_as_uint(t) << 32) | (unsigned long long)(uint32_t)j);
         };
 
-        int qn = 0;                                     /* warp-uniform */
-        const int pairs = m * n;
-        for (int p0 = 0; p0 < pairs; p0 += 32) {
-            const int p = p0 + lane;
-            int cf = 0, cb = 0, il = 0, j = 0;
-            RaySpan sp = {0, -1, 0, -1};
-            if (p < pairs) {
-                il = (int)__umulhi((uint32_t)p, magic);
-                j = p - il * n;
-                const int i = tile0 + il;
-                const float2 pi = pos[i], pj = pos[j], hd = head[i];
-                if (pair_candidates(pi.x - pj.x, pi.y - pj.y, Dir{hd.x, hd.y}, sp)) {
-                    cf = max(0, sp.fhi - sp.flo + 1);
-                    cb = max(0, sp.bhi - sp.blo + 1);
-                }
+        /* expand <= 32 queued pairs (one per lane) into single-ray tests: a warp scan of the candidate counts,
+         * then every lane of a 32-test chunk finds the pair that owns its slot by binary search over the scan
+         * (shuffles only, no divergence) and queues (observer, target, ray). */
+        int qn = 0;                                     /* pending tests, warp-uniform, < 32 between chunks */
+        auto expand = [&](uint32_t info, bool valid) {
+            const int c = valid ? (int)((info >> 5) & 31u) + (int)((info >> 13) & 15u) : 0;
+            int inc = c;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const int u = __shfl_up_sync(FULL, inc, o);
+                if (lane >= o) inc += u;
             }
-            const int c = cf + cb;
-            const uint32_t tag = ((uint32_t)il << 15) | ((uint32_t)j << 5);
-            for (int k = 0;; ++k) {
-                const bool has = k < c;
-                const unsigned mk = __ballot_sync(FULL, has);
-                if (!mk) break;
-                if (has) {
-                    const int r = k < cf ? sp.flo + k : kFwdRays + sp.blo + (k - cf);
-                    queue[qn + __popc(mk & lt)] = tag | (uint32_t)r;
+            const int total = __shfl_sync(FULL, inc, 31);
+            const int exc = inc - c;
+            for (int q0 = 0; q0 < total; q0 += 32) {
+                const int q = q0 + lane;
+                int own = 0;                            /* smallest lane with inc > q */
+#pragma unroll
+                for (int st = 16; st > 0; st >>= 1) {
+                    const int v = __shfl_sync(FULL, inc, own + st - 1);
+                    if (v <= q) own += st;
                 }
-                qn += __popc(mk);
+                const uint32_t oi = __shfl_sync(FULL, info, own);
+                const int k = q - __shfl_sync(FULL, exc, own);
+                const int ocf = (int)((oi >> 5) & 31u);
+                const int r = k < ocf ? (int)(oi & 31u) + k : kFwdRays - ocf + (int)((oi >> 10) & 7u) + k;
+                if (q < total) queue[qn + lane] = ((oi >> 17) << 5) | (uint32_t)r;
+                qn += min(32, total - q0);
                 __syncwarp();
                 if (qn >= 32) {
-                    run_tests(qn - 32, 32);
                     qn -= 32;
+                    run_tests(qn);
                     __syncwarp();
                 }
             }
+        };
+
+        int pqn = 0;                                    /* pending pairs, warp-uniform, < 32 between iterations */
+        for (int j0 = 0; j0 < n; j0 += tpi) {
+            const int j = j0 + jl;
+            uint32_t info = 0;
+            bool has = false;
+            if (on_i && j < n) {
+                const float2 pj = pos[j];
+                RaySpan sp;
+                if (pair_candidates(pi.x - pj.x, pi.y - pj.y, Dir{hd.x, hd.y}, sp)) {
+                    const int cf = max(0, sp.fhi - sp.flo + 1), cb = max(0, sp.bhi - sp.blo + 1);
+                    /* flo 0-4 | cf 5-9 | blo 10-12 | cb 13-16 | target 17-26 | observer of the tile 27-29 */
+                    info = (uint32_t)(sp.flo & 31) | ((uint32_t)cf << 5) | ((uint32_t)(sp.blo & 7) << 10) | ((uint32_t)cb << 13) |
+                           ((uint32_t)j << 17) | ((uint32_t)il << 27);
+                    has = true;
+                }
+            }
+            const unsigned bal = __ballot_sync(FULL, has);
+            if (has) pairq[pqn + __popc(bal & lt)] = info;
+            pqn += __popc(bal);
+            if (pqn >= 32) {
+                __syncwarp();
+                pqn -= 32;
+                expand(pairq[pqn + lane], true);
+            }
         }
-        if (qn > 0) run_tests(0, qn);
+        __syncwarp();
+        if (pqn > 0) expand(lane < pqn ? pairq[lane] : 0u, lane < pqn);
+        if (lane < qn) run_tests(0);
         __syncwarp();
 
         for (int idx = lane; idx < m * 8; idx += 32) {
-            const int il = idx >> 3, quad = idx & 7, i = tile0 + il;
+            const int ol = idx >> 3, quad = idx & 7, i = tile0 + ol;
             const int row = newrow[i];
             uint32_t dep = 0, sem = 0;
 #pragma unroll
             for (int k = 0; k < 4; ++k) {
-                const unsigned long long key = best[il * kSensor + quad * 4 + k];
+                const unsigned long long key = best[ol * kSensor + quad * 4 + k];
                 const bool hit = key != ~0ull;
                 const int slot = hit ? (int)(uint32_t)key : -1;
                 uint32_t dv = hit ? (uint32_t)(uint8_t)(int)__uint_as_float((uint32_t)(key >> 32)) : 255u;

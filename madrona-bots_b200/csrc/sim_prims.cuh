@@ -340,27 +340,30 @@ MBP_HD int cull_floor(float v)
 #endif
 }
 
-/* oc = observer - target, h = unit heading of the observer */
+/* oc = observer - target, h = unit heading of the observer. Cull arithmetic only: explicit FMAs are fine
+ * here (nothing below feeds a result, only the choice of which exact tests to run). */
 MBP_HD bool pair_candidates(float ocx, float ocy, Dir h, RaySpan &sp)
 {
-    const float d2 = ocx * ocx + ocy * ocy;
+    const float d2 = mb_fmaf(ocx, ocx, ocy * ocy);
     if (!(d2 >= kCullMinDist2)) return false;
     const float x = inv_sqrt_upper(d2);                          /* >= 1/D, <= 0.914 */
-    const float half = x * (1.f + 0.32f * x * x) + kCullAngleMargin;   /* >= asin(1.0005/D) on (0, 0.914] */
+    const float half = mb_fmaf(x, mb_fmaf(0.32f * x, x, 1.f), kCullAngleMargin);   /* >= asin(1.0005/D) on (0, 0.914] */
     /* direction to the target (-oc) in the heading frame: along, left */
-    const float al = -(ocx * h.x + ocy * h.y);
-    const float lf = ocx * h.y - ocy * h.x;
+    const float al = -mb_fmaf(ocx, h.x, ocy * h.y);
+    const float lf = mb_fmaf(ocx, h.y, -(ocy * h.x));
     const float rho = cull_atan2(lf, al);                         /* in [-pi, pi] */
-    const float inv_df = ((float)kFwdRays - 1.f) / (kPi * 0.5f);
-    const float inv_db = ((float)(kSensor - kFwdRays) - 1.f) / (kPi * 0.5f);
-    const float f0 = rho + kPi * 0.25f;
-    sp.flo = cull_ceil((f0 - half) * inv_df);
-    sp.fhi = cull_floor((f0 + half) * inv_df);
+    constexpr float inv_df = ((float)kFwdRays - 1.f) / (kPi * 0.5f);
+    constexpr float inv_db = ((float)(kSensor - kFwdRays) - 1.f) / (kPi * 0.5f);
+    /* ray k of a fan sits at (k / inv_d - pi/4) from the fan axis: candidates are ceil(rs - hs) .. floor(rs + hs) */
+    const float rsf = mb_fmaf(rho, inv_df, kPi * 0.25f * inv_df), hsf = half * inv_df;
+    sp.flo = cull_ceil(rsf - hsf);
+    sp.fhi = cull_floor(rsf + hsf);
     if (sp.flo < 0) sp.flo = 0;
     if (sp.fhi > kFwdRays - 1) sp.fhi = kFwdRays - 1;
-    const float rb = (rho < 0.f ? rho + kPi : rho - kPi) + kPi * 0.25f;
-    sp.blo = cull_ceil((rb - half) * inv_db);
-    sp.bhi = cull_floor((rb + half) * inv_db);
+    const float rb = rho < 0.f ? rho + kPi : rho - kPi;
+    const float rsb = mb_fmaf(rb, inv_db, kPi * 0.25f * inv_db), hsb = half * inv_db;
+    sp.blo = cull_ceil(rsb - hsb);
+    sp.bhi = cull_floor(rsb + hsb);
     if (sp.blo < 0) sp.blo = 0;
     if (sp.bhi > kSensor - kFwdRays - 1) sp.bhi = kSensor - kFwdRays - 1;
     return sp.flo <= sp.fhi || sp.blo <= sp.bhi;
