@@ -140,16 +140,16 @@ int finish(mbots_sim *s, cudaStream_t st)
     return MBOTS_OK;
 }
 
-int enqueue_repack(mbots_sim *s, cudaStream_t st, int with_sensors, int count_step, uint32_t slots)
+int enqueue_repack(mbots_sim *s, cudaStream_t st, int with_sensors, int count_step, uint32_t bound)
 {
     launch_scan(s->d, s->cur, count_step, st);
     if (s->profile && with_sensors) cudaEventRecord(s->ev[2], st);
-    launch_export(s->d, s->cur, with_sensors, slots, st);
+    const int nexp = launch_export(s->d, s->cur, with_sensors, bound, st);
     if (s->profile && with_sensors) cudaEventRecord(s->ev[3], st);
     CU(cudaGetLastError());
     CU(cudaMemcpyAsync(s->hTotals, s->d.totals, sizeof(Totals), cudaMemcpyDeviceToHost, st));
     s->cur ^= 1;
-    s->launches += 2;
+    s->launches += 1 + (uint64_t)nexp;
     s->dirty = true;
     return MBOTS_OK;
 }
@@ -159,21 +159,20 @@ int enqueue_step(mbots_sim *s, cudaStream_t st)
     if (s->profile) cudaEventRecord(s->ev[0], st);
     /* block size: the largest world known from the last synchronised step (rounded to a warp), or
      * the capacity when counts are stale because steps were enqueued without a sync in between */
-    uint32_t threads = s->d.cap, slots = s->d.cap;
+    uint32_t threads = s->d.cap, bound = 0;
     if (!s->dirty) {
         uint32_t need = s->hTotals->maxWorldCount;
         if (need < s->d.initAgents) need = s->d.initAgents;
         if (need < 32u) need = 32u;
         threads = (need + 31u) & ~31u;
-        /* a world can at most double (every agent breeds) and then refill to initAgents */
-        slots = 2u * need + s->d.initAgents;
-        slots = (slots + 15u) & ~15u;
-        if (slots > s->d.cap) slots = s->d.cap;
+        /* what the export kernel's fast variant is sized for; a world that outgrows it in this one step
+         * (it could double) is picked up by the full variant */
+        bound = need + 8u;
     }
     launch_step(s->d, s->cur, threads, st);
     if (s->profile) cudaEventRecord(s->ev[1], st);
     s->launches += 1;
-    int rc = enqueue_repack(s, st, 1, 1, slots);
+    int rc = enqueue_repack(s, st, 1, 1, bound);
     if (rc != MBOTS_OK) return rc;
     if (s->profile) {
         CU(cudaEventSynchronize(s->ev[3]));
@@ -232,14 +231,14 @@ int mbots_create_ex(const mbots_config *cfg, mbots_sim **out)
         for (auto &ev : s->evShift) if (cudaEventCreate(&ev) != cudaSuccess) rc = fail(MBOTS_ECUDA, "cudaEventCreate");
     }
     if (rc == MBOTS_OK) {
-        size_t sm1 = step_smem_bytes(cap), sm2 = export_smem_bytes(cap);
+        size_t sm1 = step_smem_bytes(cap), sm2 = export_smem_bytes(cap, 8, false);
         (void)sm1; (void)sm2;   /* both far below the 48 KB default limit for cap <= 1024 */
         /* Sim::Sim for every world, then the first row assignment (no sensor pass: the
          * reference's tensors are only meaningful after the first step()). */
         launch_init(s->d, 0);
         s->cur = 0;
         s->launches = 1;
-        rc = enqueue_repack(s, 0, 0, 0, s->d.cap);
+        rc = enqueue_repack(s, 0, 0, 0, 0);
         if (rc == MBOTS_OK) rc = finish(s, 0);
     }
     if (rc != MBOTS_OK) { free_all(s); delete s; return rc; }

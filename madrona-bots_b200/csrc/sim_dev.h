@@ -81,11 +81,11 @@ struct SimDev {
 void launch_init(const SimDev &d, cudaStream_t s);
 void launch_step(const SimDev &d, int cur, uint32_t threads, cudaStream_t s);
 void launch_scan(const SimDev &d, int cur, int count_step, cudaStream_t s);
-void launch_export(const SimDev &d, int cur, int with_sensors, uint32_t slots, cudaStream_t s);
+int launch_export(const SimDev &d, int cur, int with_sensors, uint32_t bound, cudaStream_t s);
 void launch_shift(const SimDev &d, int cur, uint32_t rows_upper, cudaStream_t s);
 void launch_stats_reduce(const SimDev &d, long long *out16, cudaStream_t s);
 void launch_debug_gather(const SimDev &d, int what, void *out, cudaStream_t s);
 size_t step_smem_bytes(uint32_t cap);
-size_t export_smem_bytes(uint32_t slots);
+size_t export_smem_bytes(uint32_t slots, uint32_t tile, bool fast);
 
 } // namespace mbk

@@ -526,20 +526,49 @@ __global__ void __launch_bounds__(kScanTile) scan_kernel(SimDev d, int cur, int 
 /* export_kernel: one WARP per world, kExportWarps independent worlds per CTA.  */
 /* No block barriers: every phase of a world is synchronised with __syncwarp,   */
 /* so warps drift apart and hide each other's memory latency.                   */
+/*                                                                             */
+/* Two instantiations share the code:                                          */
+/*   FAST  worlds of at most `slots` <= 64 agents (every world of a normal     */
+/*         rollout). Nearest hits are 32-bit keys -- (t bits - bits(1.0f)) in   */
+/*         26 bits, target slot in 6 -- so one native shared-memory atomicMin   */
+/*         keeps them, and the keys of `tile` <= 64 observers fit beside the    */
+/*         agent arrays: a whole world is one sensor tile.                      */
+/*   full  any world up to the capacity (<= 1024): 64-bit keys, 8 observers per */
+/*         tile. Launched after the FAST kernel for the worlds it skipped, and  */
+/*         alone when the host has no fresh bound on the population.            */
 
 constexpr int kExportWarps = 4;
-constexpr int kSenseTile = 8;        /* observers per sensor pass of a warp */
 constexpr int kQueue = 64;           /* pending pairs / pending exact tests of a warp: < 32 carried over, + <= 32 pushed */
+constexpr int kFastSlots = 64;       /* 6 slot bits in a 32-bit key */
+constexpr int kFullTile = 8;
 
-/* per-warp shared memory: agent arrays sized for `slots` agents + one sensor tile */
+template <bool FAST> struct Sense;
+template <> struct Sense<true> {
+    typedef uint32_t Key;
+    static constexpr int kJBits = 6;
+    static constexpr uint32_t kMiss = 0xffffffffu;
+    static __device__ __forceinline__ Key make(float t, int j) { return ((__float_as_uint(t) - 0x3f800000u) << 6) | (uint32_t)j; }
+    static __device__ __forceinline__ int slot(Key k) { return (int)(k & 63u); }
+    static __device__ __forceinline__ float t(Key k) { return __uint_as_float((k >> 6) + 0x3f800000u); }
+};
+template <> struct Sense<false> {
+    typedef unsigned long long Key;
+    static constexpr int kJBits = 10;
+    static constexpr unsigned long long kMiss = ~0ull;
+    static __device__ __forceinline__ Key make(float t, int j) { return ((Key)__float_as_uint(t) << 32) | (Key)(uint32_t)j; }
+    static __device__ __forceinline__ int slot(Key k) { return (int)(uint32_t)k; }
+    static __device__ __forceinline__ float t(Key k) { return __uint_as_float((uint32_t)(k >> 32)); }
+};
+
+/* per-warp shared memory: agent arrays sized for `slots` agents + the keys of one sensor tile */
 struct ExportLayout {
     uint32_t best, pos, head, queue, pairq, newrow, oldrow, theta, spec, total;
 };
-__host__ __device__ inline ExportLayout export_layout(uint32_t slots)
+__host__ __device__ inline ExportLayout export_layout(uint32_t slots, uint32_t tile, uint32_t key_bytes)
 {
     ExportLayout L;
     uint32_t o = 0;
-    L.best = o; o += kSenseTile * kSensor * 8;          /* u64, 8-byte aligned first */
+    L.best = o; o += tile * kSensor * key_bytes;        /* 16-byte aligned first */
     L.pos = o; o += slots * 8;                          /* float2 */
     L.head = o; o += slots * 8;                         /* float2 unit heading (cull only) */
     L.queue = o; o += kQueue * 4;
@@ -552,7 +581,10 @@ __host__ __device__ inline ExportLayout export_layout(uint32_t slots)
     return L;
 }
 
-size_t export_smem_bytes(uint32_t slots) { return (size_t)export_layout(slots).total * kExportWarps; }
+size_t export_smem_bytes(uint32_t slots, uint32_t tile, bool fast)
+{
+    return (size_t)export_layout(slots, tile, fast ? 4u : 8u).total * kExportWarps;
+}
 
 /* Copy one column of every agent of the world from its old row to its new row; lanes run over
  * (agent, part) so that consecutive lanes touch consecutive bytes. V = bytes per lane access,
@@ -586,15 +618,16 @@ __device__ __forceinline__ void carry_column(void *dst, const void *src, const i
     }
 }
 
-__global__ void __launch_bounds__(kExportWarps * 32) export_kernel(SimDev d, int cur, int with_sensors, uint32_t slots)
+/* One world, one warp. `my` = this warp's shared memory (export_layout). */
+template <bool FAST>
+__device__ __forceinline__ void export_world(const SimDev &d, int cur, int with_sensors, uint32_t slots, uint32_t tile,
+                                             uint32_t w, int n, unsigned char *my)
 {
-    extern __shared__ __align__(16) unsigned char smem_raw[];
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const uint32_t w = blockIdx.x * kExportWarps + warp;
-    if (w >= d.numWorlds) return;                       /* whole warp: no block-level barrier below */
-    const ExportLayout L = export_layout(slots);
-    unsigned char *my = smem_raw + (size_t)L.total * warp;
-    unsigned long long *best = reinterpret_cast<unsigned long long *>(my + L.best);
+    typedef Sense<FAST> S;
+    typedef typename S::Key Key;
+    const int lane = threadIdx.x & 31;
+    const ExportLayout L = export_layout(slots, tile, sizeof(Key));
+    Key *best = reinterpret_cast<Key *>(my + L.best);
     float2 *pos = reinterpret_cast<float2 *>(my + L.pos);
     float2 *head = reinterpret_cast<float2 *>(my + L.head);
     uint32_t *queue = reinterpret_cast<uint32_t *>(my + L.queue);
@@ -607,7 +640,6 @@ __global__ void __launch_bounds__(kExportWarps * 32) export_kernel(SimDev d, int
     const size_t base = (size_t)w * d.cap;
     const ObsSet &from = d.obs[cur];
     const ObsSet &to = d.obs[cur ^ 1];
-    const int n = d.worldCount[w];
     const int4 rb = d.rowBase[cur ^ 1][w];
     const int off = d.worldOffset[w];
     const float4 srew = d.speciesReward[w];
@@ -685,45 +717,42 @@ __global__ void __launch_bounds__(kExportWarps * 32) export_kernel(SimDev d, int
 
     if (!with_sensors) return;
 
-    /* ---- sensor (M/src/mw/device/bvh_raycast.cpp:193-305), observers in tiles of kSenseTile:
-     *  1. lanes form a (observer of the tile) x (target) grid -- 8 x 4 for a full tile, narrower for the last
-     *     partial tile -- so a lane keeps its observer in registers and steps through the targets with no
-     *     index arithmetic. Per pair: conservative candidate rays (pair_candidates, ~0.27 per pair).
-     *     Candidates are ragged, so they are not tested in place: a warp scan gives every lane its place in a
-     *     per-warp queue of (observer, target, ray), and whenever 32 are pending the warp runs the exact
-     *     test on 32 of them at full lane occupancy.
-     *  2. exact test (make_ray + ray/sphere, the oracle's arithmetic): nearest accepted hit kept
-     *     with a 64-bit shared-memory atomicMin on (t bits << 32 | target slot) -- ties go to
-     *     the lowest slot, and the order in which candidates are tested does not matter.
-     *  3. one lane per (observer, 4 rays): decode, write 4 depth + 4 semantic bytes, finder hit */
-    for (int tile0 = 0; tile0 < n; tile0 += kSenseTile) {
-        const int m = min(kSenseTile, n - tile0);
+    /* ---- sensor (M/src/mw/device/bvh_raycast.cpp:193-305). Observers in tiles of `tile` (FAST: the whole world):
+     *  1. cull. Within a tile, blocks of <= 32 observers are spread over the lanes as an (observer x target)
+     *     grid -- 32 x 1, or for the last few observers 8 x 4 ... 1 x 32 -- so a lane keeps its observer in
+     *     registers and steps through the targets with no index arithmetic. Per pair: conservative candidate
+     *     rays (pair_candidates, ~0.27 per pair). Pairs with candidates are ballot-compacted into a pair queue.
+     *  2. expand. 32 queued pairs at a time: a warp scan of their candidate counts, then every lane of a
+     *     32-test chunk finds the pair that owns its slot by binary search over the scan (shuffles only, no
+     *     divergence) and queues (observer, target, ray).
+     *  3. exact test, 32 queued candidates at full lane occupancy (make_ray + ray/sphere, the oracle's
+     *     arithmetic): nearest accepted hit kept with a shared-memory atomicMin on (t bits, target slot) --
+     *     ties go to the lowest slot, and the order in which candidates are tested does not matter.
+     *  4. one lane per (observer, 4 rays): decode, write 4 depth + 4 semantic bytes, finder hit */
+    constexpr int JB = S::kJBits;
+    for (int tile0 = 0; tile0 < n; tile0 += (int)tile) {
+        const int m = min((int)tile, n - tile0);
         {
-            ulonglong2 *b2 = reinterpret_cast<ulonglong2 *>(best);
-            for (int idx = lane; idx < m * (kSensor / 2); idx += 32) b2[idx] = make_ulonglong2(~0ull, ~0ull);
+            uint4 *b4 = reinterpret_cast<uint4 *>(best);
+            const int vecs = m * kSensor * (int)sizeof(Key) / 16;
+            for (int idx = lane; idx < vecs; idx += 32) b4[idx] = make_uint4(~0u, ~0u, ~0u, ~0u);
         }
-        const int lg = m > 4 ? 3 : m > 2 ? 2 : m > 1 ? 1 : 0;   /* observers across lanes: 1 << lg >= m */
-        const int il = lane & ((1 << lg) - 1), jl = lane >> lg, tpi = 32 >> lg;
-        const bool on_i = il < m;
-        const float2 pi = pos[tile0 + (on_i ? il : 0)], hd = head[tile0 + (on_i ? il : 0)];
         __syncwarp();
 
-        auto run_tests = [&](int first) {
-            const uint32_t e = queue[first + lane];
-            const int r = (int)(e & 31u), j = (int)((e >> 5) & 1023u), ql = (int)(e >> 15);
-            const float2 qi = pos[tile0 + ql], qj = pos[j];
-            const Ray ray = make_ray(theta[tile0 + ql], r);
-            float t;
-            if (ray_sphere(ray, qi.x - qj.x, qi.y - qj.y, t) && t > kNearSphere)
-                atomicMin(&best[ql * kSensor + r],
-                          ((unsigned long long)__float_as_uint(t) << 32) | (unsigned long long)(uint32_t)j);
-        };
-
-        /* expand <= 32 queued pairs (one per lane) into single-ray tests: a warp scan of the candidate counts,
-         * then every lane of a 32-test chunk finds the pair that owns its slot by binary search over the scan
-         * (shuffles only, no divergence) and queues (observer, target, ray). */
         int qn = 0;                                     /* pending tests, warp-uniform, < 32 between chunks */
-        auto expand = [&](uint32_t info, bool valid) {
+        auto run_tests = [&](int first, int count) {
+            if (lane < count) {
+                const uint32_t e = queue[first + lane];
+                const int r = (int)(e & 31u), j = (int)((e >> 5) & ((1u << JB) - 1u)), ol = (int)(e >> (5 + JB));
+                const float2 qi = pos[tile0 + ol], qj = pos[j];
+                const Ray ray = make_ray(theta[tile0 + ol], r);
+                float t;
+                if (ray_sphere(ray, qi.x - qj.x, qi.y - qj.y, t) && t > kNearSphere)
+                    atomicMin(&best[ol * kSensor + r], S::make(t, j));
+            }
+        };
+        /* `flush`: also run a last partial chunk of tests */
+        auto expand = [&](uint32_t info, bool valid, bool flush) {
             const int c = valid ? (int)((info >> 5) & 31u) + (int)((info >> 13) & 15u) : 0;
             int inc = c;
 #pragma unroll
@@ -733,7 +762,7 @@ __global__ void __launch_bounds__(kExportWarps * 32) export_kernel(SimDev d, int
             }
             const int total = __shfl_sync(FULL, inc, 31);
             const int exc = inc - c;
-            for (int q0 = 0; q0 < total; q0 += 32) {
+            for (int q0 = 0; q0 < total || (flush && qn > 0); q0 += 32) {
                 const int q = q0 + lane;
                 int own = 0;                            /* smallest lane with inc > q */
 #pragma unroll
@@ -746,56 +775,64 @@ __global__ void __launch_bounds__(kExportWarps * 32) export_kernel(SimDev d, int
                 const int ocf = (int)((oi >> 5) & 31u);
                 const int r = k < ocf ? (int)(oi & 31u) + k : kFwdRays - ocf + (int)((oi >> 10) & 7u) + k;
                 if (q < total) queue[qn + lane] = ((oi >> 17) << 5) | (uint32_t)r;
-                qn += min(32, total - q0);
+                qn += max(0, min(32, total - q0));
                 __syncwarp();
-                if (qn >= 32) {
-                    qn -= 32;
-                    run_tests(qn);
+                const bool last = q0 + 32 >= total;
+                if (qn >= 32 || (flush && last)) {
+                    const int cnt = min(32, qn);
+                    qn -= cnt;
+                    run_tests(qn, cnt);
                     __syncwarp();
                 }
             }
         };
 
         int pqn = 0;                                    /* pending pairs, warp-uniform, < 32 between iterations */
-        for (int j0 = 0; j0 < n; j0 += tpi) {
-            const int j = j0 + jl;
-            uint32_t info = 0;
-            bool has = false;
-            if (on_i && j < n) {
-                const float2 pj = pos[j];
-                RaySpan sp;
-                if (pair_candidates(pi.x - pj.x, pi.y - pj.y, Dir{hd.x, hd.y}, sp)) {
-                    const int cf = max(0, sp.fhi - sp.flo + 1), cb = max(0, sp.bhi - sp.blo + 1);
-                    /* flo 0-4 | cf 5-9 | blo 10-12 | cb 13-16 | target 17-26 | observer of the tile 27-29 */
-                    info = (uint32_t)(sp.flo & 31) | ((uint32_t)cf << 5) | ((uint32_t)(sp.blo & 7) << 10) | ((uint32_t)cb << 13) |
-                           ((uint32_t)j << 17) | ((uint32_t)il << 27);
-                    has = true;
+        for (int sub0 = 0; sub0 < m; sub0 += 32) {
+            const int ms = min(32, m - sub0);
+            const int lg = ms > 16 ? 5 : ms > 8 ? 4 : ms > 4 ? 3 : ms > 2 ? 2 : ms > 1 ? 1 : 0;   /* 1 << lg >= ms */
+            const int il = lane & ((1 << lg) - 1), jl = lane >> lg, tpi = 32 >> lg;
+            const bool on_i = il < ms;
+            const int ol = sub0 + (on_i ? il : 0);      /* observer within the tile */
+            const float2 pi = pos[tile0 + ol], hd = head[tile0 + ol];
+            for (int j0 = 0; j0 < n; j0 += tpi) {
+                const int j = j0 + jl;
+                const float2 pj = pos[min(j, n - 1)];
+                const RayCount rc = pair_spans(pi.x - pj.x, pi.y - pj.y, Dir{hd.x, hd.y});
+                /* flo 0-4 | cf 5-9 | blo 10-12 | cb 13-16 | target 17.. (JB bits) | observer of the tile */
+                const uint32_t info = (uint32_t)(rc.flo & 31) | ((uint32_t)rc.cf << 5) | ((uint32_t)(rc.blo & 7) << 10) |
+                                      ((uint32_t)rc.cb << 13) | ((uint32_t)j << 17) | ((uint32_t)ol << (17 + JB));
+                const bool has = on_i && j < n && (rc.cf + rc.cb) > 0;
+                const unsigned bal = __ballot_sync(FULL, has);
+                if (has) pairq[pqn + __popc(bal & lt)] = info;
+                pqn += __popc(bal);
+                if (pqn >= 32) {
+                    __syncwarp();
+                    pqn -= 32;
+                    expand(pairq[pqn + lane], true, false);
                 }
-            }
-            const unsigned bal = __ballot_sync(FULL, has);
-            if (has) pairq[pqn + __popc(bal & lt)] = info;
-            pqn += __popc(bal);
-            if (pqn >= 32) {
-                __syncwarp();
-                pqn -= 32;
-                expand(pairq[pqn + lane], true);
             }
         }
         __syncwarp();
-        if (pqn > 0) expand(lane < pqn ? pairq[lane] : 0u, lane < pqn);
-        if (lane < qn) run_tests(0);
-        __syncwarp();
+        expand(lane < pqn ? pairq[lane] : 0u, lane < pqn, true);
 
         for (int idx = lane; idx < m * 8; idx += 32) {
             const int ol = idx >> 3, quad = idx & 7, i = tile0 + ol;
             const int row = newrow[i];
+            Key key[4];
+            if (FAST) {
+                const uint4 v = reinterpret_cast<const uint4 *>(best)[idx];
+                key[0] = (Key)v.x; key[1] = (Key)v.y; key[2] = (Key)v.z; key[3] = (Key)v.w;
+            } else {
+#pragma unroll
+                for (int k = 0; k < 4; ++k) key[k] = best[idx * 4 + k];
+            }
             uint32_t dep = 0, sem = 0;
 #pragma unroll
             for (int k = 0; k < 4; ++k) {
-                const unsigned long long key = best[ol * kSensor + quad * 4 + k];
-                const bool hit = key != ~0ull;
-                const int slot = hit ? (int)(uint32_t)key : -1;
-                uint32_t dv = hit ? (uint32_t)(uint8_t)(int)__uint_as_float((uint32_t)(key >> 32)) : 255u;
+                const bool hit = key[k] != S::kMiss;
+                const int slot = hit ? S::slot(key[k]) : -1;
+                uint32_t dv = hit ? (uint32_t)(uint8_t)(int)S::t(key[k]) : 255u;
                 const uint32_t sv = hit ? (uint32_t)spec[slot] : 0xffu;
                 if (quad == 0 && k == 0) dv = (uint32_t)row & 0xffu;      /* "sanity" overwrite (U9) */
                 if (quad == kFinderRay / 4 && k == kFinderRay % 4) d.target[base + i] = (int16_t)slot;
@@ -806,6 +843,33 @@ __global__ void __launch_bounds__(kExportWarps * 32) export_kernel(SimDev d, int
             reinterpret_cast<uint32_t *>(to.semantic)[(size_t)row * 8 + quad] = sem;
         }
         __syncwarp();
+    }
+}
+
+/* skip: FAST -> worlds with more than `slots` agents are left to the full kernel;
+ *       full -> worlds with at most `skip_upto` agents were done by the FAST kernel (grid-stride over the
+ *               worlds with a small grid, and nothing at all when no world is that large). */
+template <bool FAST>
+__global__ void __launch_bounds__(kExportWarps * 32, FAST ? 7 : 4)
+export_kernel(SimDev d, int cur, int with_sensors, uint32_t slots, uint32_t tile, int skip_upto)
+{
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    const int warp = threadIdx.x >> 5;
+    if (!FAST && skip_upto >= 0 && (int)d.totals->maxWorldCount <= skip_upto) return;
+    unsigned char *my = smem_raw + (size_t)export_layout(slots, tile, sizeof(typename Sense<FAST>::Key)).total * warp;
+    if (FAST) {                                     /* one world per warp */
+        const uint32_t w = blockIdx.x * kExportWarps + warp;
+        if (w >= d.numWorlds) return;               /* whole warp: no block-level barrier anywhere */
+        const int n = d.worldCount[w];
+        if (n > (int)slots) return;
+        export_world<FAST>(d, cur, with_sensors, slots, tile, w, n, my);
+    } else {
+        for (uint32_t w = blockIdx.x * kExportWarps + warp; w < d.numWorlds; w += gridDim.x * kExportWarps) {
+            const int n = d.worldCount[w];
+            if (n <= skip_upto) continue;
+            export_world<FAST>(d, cur, with_sensors, slots, tile, w, n, my);
+            __syncwarp();
+        }
     }
 }
 
@@ -909,14 +973,34 @@ void launch_scan(const SimDev &d, int cur, int count_step, cudaStream_t s)
     scan_kernel<<<(d.numWorlds + kScanTile - 1) / kScanTile, kScanTile, 0, s>>>(d, cur, count_step);
 }
 
-void launch_export(const SimDev &d, int cur, int with_sensors, uint32_t slots, cudaStream_t s)
+template <bool FAST>
+static void launch_export_variant(const SimDev &d, int cur, int with_sensors, uint32_t slots, uint32_t tile, int skip_upto,
+                                  cudaStream_t s)
 {
-    /* slots: per-warp staging capacity, >= the largest world; the capacity always is */
-    if (slots == 0 || slots > d.cap) slots = d.cap;
-    const size_t smem = export_smem_bytes(slots);
+    const size_t smem = export_smem_bytes(slots, tile, FAST);
     if (smem > 48 * 1024)
-        cudaFuncSetAttribute(export_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    export_kernel<<<(d.numWorlds + kExportWarps - 1) / kExportWarps, kExportWarps * 32, smem, s>>>(d, cur, with_sensors, slots);
+        cudaFuncSetAttribute(export_kernel<FAST>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    uint32_t grid = (d.numWorlds + kExportWarps - 1) / kExportWarps;
+    if (!FAST && skip_upto >= 0 && grid > 148u * 4u) grid = 148u * 4u;   /* clean-up pass: few worlds, if any */
+    export_kernel<FAST><<<grid, kExportWarps * 32, smem, s>>>(d, cur, with_sensors, slots, tile, skip_upto);
+}
+
+/* bound: the largest world the caller expects after this step (0 = unknown). Worlds above it are still
+ * handled -- by the full kernel -- so a wrong bound costs time, never correctness. Returns the launches made. */
+int launch_export(const SimDev &d, int cur, int with_sensors, uint32_t bound, cudaStream_t s)
+{
+    uint32_t fast_slots = (bound + 7u) & ~7u;
+    if (bound == 0 || fast_slots > (uint32_t)kFastSlots || fast_slots > d.cap) {
+        launch_export_variant<false>(d, cur, with_sensors, d.cap, kFullTile, -1, s);
+        return 1;
+    }
+    /* one tile = the whole world for all but the largest worlds */
+    uint32_t tile = d.initAgents + 8u;
+    if (tile < 40u) tile = 40u;
+    if (tile > fast_slots) tile = fast_slots;
+    launch_export_variant<true>(d, cur, with_sensors, fast_slots, tile, 0, s);
+    launch_export_variant<false>(d, cur, with_sensors, d.cap, kFullTile, (int)fast_slots, s);
+    return 2;
 }
 
 void launch_shift(const SimDev &d, int cur, uint32_t rows_upper, cudaStream_t s)

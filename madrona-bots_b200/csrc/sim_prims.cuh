@@ -341,12 +341,16 @@ MBP_HD int cull_floor(float v)
 }
 
 /* oc = observer - target, h = unit heading of the observer. Cull arithmetic only: explicit FMAs are fine
- * here (nothing below feeds a result, only the choice of which exact tests to run). */
-MBP_HD bool pair_candidates(float ocx, float ocy, Dir h, RaySpan &sp)
+ * here (nothing below feeds a result, only the choice of which exact tests to run). Straight-line code (the
+ * kernel runs it on every lane of a warp): returns the forward span [flo, flo + cf) and the backward span
+ * [blo, blo + cb) as counts; both counts are 0 for a pair that cannot produce an accepted hit. */
+struct RayCount { int flo, cf, blo, cb; };
+
+MBP_HD RayCount pair_spans(float ocx, float ocy, Dir h)
 {
     const float d2 = mb_fmaf(ocx, ocx, ocy * ocy);
-    if (!(d2 >= kCullMinDist2)) return false;
-    const float x = inv_sqrt_upper(d2);                          /* >= 1/D, <= 0.914 */
+    const bool far_enough = d2 >= kCullMinDist2;                 /* false also for NaN */
+    const float x = inv_sqrt_upper(far_enough ? d2 : kCullMinDist2);   /* >= 1/D, <= 0.914 */
     const float half = mb_fmaf(x, mb_fmaf(0.32f * x, x, 1.f), kCullAngleMargin);   /* >= asin(1.0005/D) on (0, 0.914] */
     /* direction to the target (-oc) in the heading frame: along, left */
     const float al = -mb_fmaf(ocx, h.x, ocy * h.y);
@@ -356,17 +360,27 @@ MBP_HD bool pair_candidates(float ocx, float ocy, Dir h, RaySpan &sp)
     constexpr float inv_db = ((float)(kSensor - kFwdRays) - 1.f) / (kPi * 0.5f);
     /* ray k of a fan sits at (k / inv_d - pi/4) from the fan axis: candidates are ceil(rs - hs) .. floor(rs + hs) */
     const float rsf = mb_fmaf(rho, inv_df, kPi * 0.25f * inv_df), hsf = half * inv_df;
-    sp.flo = cull_ceil(rsf - hsf);
-    sp.fhi = cull_floor(rsf + hsf);
-    if (sp.flo < 0) sp.flo = 0;
-    if (sp.fhi > kFwdRays - 1) sp.fhi = kFwdRays - 1;
+    int flo = cull_ceil(rsf - hsf), fhi = cull_floor(rsf + hsf);
+    flo = flo < 0 ? 0 : flo;
+    fhi = fhi > kFwdRays - 1 ? kFwdRays - 1 : fhi;
     const float rb = rho < 0.f ? rho + kPi : rho - kPi;
     const float rsb = mb_fmaf(rb, inv_db, kPi * 0.25f * inv_db), hsb = half * inv_db;
-    sp.blo = cull_ceil(rsb - hsb);
-    sp.bhi = cull_floor(rsb + hsb);
-    if (sp.blo < 0) sp.blo = 0;
-    if (sp.bhi > kSensor - kFwdRays - 1) sp.bhi = kSensor - kFwdRays - 1;
-    return sp.flo <= sp.fhi || sp.blo <= sp.bhi;
+    int blo = cull_ceil(rsb - hsb), bhi = cull_floor(rsb + hsb);
+    blo = blo < 0 ? 0 : blo;
+    bhi = bhi > kSensor - kFwdRays - 1 ? kSensor - kFwdRays - 1 : bhi;
+    RayCount rc;
+    rc.flo = flo; rc.blo = blo;
+    rc.cf = far_enough && fhi >= flo ? fhi - flo + 1 : 0;
+    rc.cb = far_enough && bhi >= blo ? bhi - blo + 1 : 0;
+    return rc;
+}
+
+MBP_HD bool pair_candidates(float ocx, float ocy, Dir h, RaySpan &sp)
+{
+    const RayCount rc = pair_spans(ocx, ocy, h);
+    sp.flo = rc.flo; sp.fhi = rc.flo + rc.cf - 1;
+    sp.blo = rc.blo; sp.bhi = rc.blo + rc.cb - 1;
+    return rc.cf + rc.cb > 0;
 }
 
 } // namespace mbp
