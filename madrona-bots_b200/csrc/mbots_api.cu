@@ -100,7 +100,7 @@ int alloc_all(mbots_sim *s)
     SimDev &d = s->d;
     const size_t W = d.numWorlds, rows = W * d.cap;
     ALLOC(d.pose, rows); ALLOC(d.health, rows); ALLOC(d.species, rows); ALLOC(d.target, rows);
-    ALLOC(d.scratch, rows);
+    ALLOC(d.scratch, rows); ALLOC(d.row, rows);
     ALLOC(d.worldCount, W); ALLOC(d.worldOffset, W); ALLOC(d.rngKey, W); ALLOC(d.rngCount, W);
     ALLOC(d.numFood, W); ALLOC(d.food, W * 48);
     ALLOC(d.speciesLive, W); ALLOC(d.rowBase[0], W); ALLOC(d.rowBase[1], W);

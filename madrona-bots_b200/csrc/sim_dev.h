@@ -53,6 +53,7 @@ struct SimDev {
     uint8_t *species;         /* 1..4 */
     int16_t *target;          /* finder hit of the last sensor pass: slot in own world, -1 none */
     float4 *scratch;          /* step -> export hand-off: old row (int bits), surr.x, surr.y, stat bits */
+    int32_t *row;             /* export -> step hand-off: the agent's observation row in the current set */
 
     /* per world */
     int32_t *worldCount;      /* live agents */
@@ -79,13 +80,13 @@ struct SimDev {
 
 /* launchers (sim_kernels.cu) */
 void launch_init(const SimDev &d, cudaStream_t s);
-void launch_step(const SimDev &d, int cur, uint32_t threads, cudaStream_t s);
+void launch_step(const SimDev &d, int cur, uint32_t slots, cudaStream_t s);
 void launch_scan(const SimDev &d, int cur, int count_step, cudaStream_t s);
 int launch_export(const SimDev &d, int cur, int with_sensors, uint32_t bound, cudaStream_t s);
 void launch_shift(const SimDev &d, int cur, uint32_t rows_upper, cudaStream_t s);
 void launch_stats_reduce(const SimDev &d, long long *out16, cudaStream_t s);
 void launch_debug_gather(const SimDev &d, int what, void *out, cudaStream_t s);
-size_t step_smem_bytes(uint32_t cap);
+size_t step_smem_bytes(uint32_t slots);
 size_t export_smem_bytes(uint32_t slots, uint32_t tile, bool fast);
 
 } // namespace mbk

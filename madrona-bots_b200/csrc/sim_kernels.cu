@@ -34,37 +34,6 @@ using namespace mbp;
 /* ------------------------------------------------------------------------- */
 /* small block-level helpers                                                   */
 
-/* Rank of this thread among lower threads of the same species (sp in 0..3, or -1 for
- * "not an agent"), and the per-species totals. `wc` is a shared uint32[32] (8 bits per
- * species per warp), written once per kernel. One barrier. */
-__device__ __forceinline__ int block_species_rank(int sp, int tot[4], uint32_t *wc)
-{
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nw = (blockDim.x + 31) >> 5;
-    const unsigned lt = (1u << lane) - 1u;
-    uint32_t packed = 0;
-    int in_warp = 0;
-#pragma unroll
-    for (int k = 0; k < 4; ++k) {
-        const unsigned b = __ballot_sync(FULL, sp == k);
-        packed |= (uint32_t)__popc(b) << (8 * k);   /* <= 32 per warp: fits 8 bits */
-        if (sp == k) in_warp = __popc(b & lt);
-    }
-    if (lane == 0) wc[warp] = packed;
-    __syncthreads();
-    int base = 0;
-    tot[0] = tot[1] = tot[2] = tot[3] = 0;
-    for (int i = 0; i < nw; ++i) {
-        const uint32_t p = wc[i];
-#pragma unroll
-        for (int k = 0; k < 4; ++k) {
-            const int c = (int)((p >> (8 * k)) & 0xffu);
-            tot[k] += c;
-            if (i < warp && sp == k) base += c;
-        }
-    }
-    return base + in_warp;
-}
-
 __device__ __forceinline__ int comp(const int4 &v, int k)
 {
     return k == 0 ? v.x : k == 1 ? v.y : k == 2 ? v.z : v.w;
@@ -110,61 +79,36 @@ __global__ void init_kernel(SimDev d)
 }
 
 /* ------------------------------------------------------------------------- */
-/* step_kernel                                                                 */
+/* step_kernel: one WARP per world, kStepWarps independent worlds per CTA.     */
+/* No block barriers. Agents are taken 32 at a time (one or two passes for a   */
+/* normal world); what an agent needs in a later phase is parked in this       */
+/* warp's shared memory, cross-agent effects are shared-memory atomics, and    */
+/* every count / rank is a ballot + popc or a warp reduction.                  */
 
-struct StepShared {
-    uint32_t chunkAgents[kNumChunks];
-    uint32_t chunkSpeed[kNumChunks];
-    uint2 food[kNumChunks];
-    Key draws[32];
-    uint32_t wcs[32];
-    uint32_t xch0[32], xch1[32];
-    uint32_t cnt[4], hsum[4];
-    uint32_t rngCount;
-    int32_t numFood;
-    uint32_t foodDirty, eaten, shots;
-    /* followed by: int accum[cap]; uint32 wantKey[cap]; uint32 wantMask[cap/32]; uint32 ateMask[cap/32]; uint8 species[cap] */
-};
+constexpr int kStepWarps = 4;
 
-size_t step_smem_bytes(uint32_t cap)
+/* per-warp shared memory, sized for `slots` >= the largest world before the step */
+struct StepLayout { uint32_t chunkAgents, chunkSpeed, food, pose, accum, oldrow, info, spec, total; };
+__host__ __device__ inline StepLayout step_layout(uint32_t slots)
 {
-    return sizeof(StepShared) + (size_t)cap * (4 + 4 + 1) + (size_t)(cap / 32) * 8 + 16;
+    StepLayout L;
+    uint32_t o = 0;
+    L.pose = o; o += slots * 16;                        /* float4 x, y, rot.w, rot.z (after the move) */
+    L.food = o; o += kNumChunks * 8;
+    L.chunkAgents = o; o += kNumChunks * 4;
+    L.chunkSpeed = o; o += kNumChunks * 4;
+    L.accum = o; o += slots * 4;                        /* HealthAccumulator */
+    L.oldrow = o; o += slots * 4;
+    L.info = o; o += slots * 4;
+    L.spec = o; o += (slots + 15u) & ~15u;
+    L.total = (o + 15u) & ~15u;
+    return L;
 }
 
-/* addFoodSystem + addFoodToChunk (src/sim/sim.cpp:308-387) for one world, executed by
- * one thread from 32 pre-split draw keys (the stream is counter-based, so draw k is
- * split_i(key, count + k) whatever happened before it). At most 2 + 3*7 = 23 draws. */
-__device__ __forceinline__ void add_food(StepShared &sh)
-{
-    uint32_t k = 0;
-    if (key_sample_i32(sh.draws[k++], 0, 10) == 0) {
-        uint32_t n = (uint32_t)key_sample_i32(sh.draws[k++], 1, 3);
-        const uint32_t allowed = (uint32_t)kTotalAllowedFood - (uint32_t)sh.numFood;   /* unsigned, U12 */
-        n = n < allowed ? n : allowed;
-        for (uint32_t i = 0; i < n; ++i) {
-            const uint32_t cx = (uint32_t)key_sample_i32(sh.draws[k++], 0, kChunksX);
-            const uint32_t cy = (uint32_t)key_sample_i32(sh.draws[k++], 0, kChunksY);
-            k += 2;                                     /* two discarded draws (:311-312) */
-            uint2 f = sh.food[cx + cy * kChunksX];
-            const uint32_t mask = (f.y >> 8) & 0x1fu;
-            if (mask != 0x1fu) {
-                const uint32_t p = (uint32_t)__ffs((int)(~mask & 0x1fu)) - 1u;   /* first empty package */
-                const uint32_t rx = (uint32_t)key_sample_i32(sh.draws[k++], 0, kChunkWidth);
-                const uint32_t ry = (uint32_t)key_sample_i32(sh.draws[k++], 0, kChunkWidth);
-                k += 1;                                 /* yaw of the render-only food entity (:340) */
-                const uint32_t cell = (rx << 4) | ry;
-                if (p < 4u) f.x = (f.x & ~(0xffu << (8 * p))) | (cell << (8 * p));
-                else f.y = (f.y & ~0xffu) | cell;
-                f.y |= 1u << (8 + p);
-                sh.food[cx + cy * kChunksX] = f;
-                sh.numFood += 1;
-                sh.foodDirty = 1;
-            }
-        }
-    }
-    sh.rngCount += k;
-}
+size_t step_smem_bytes(uint32_t slots) { return (size_t)step_layout(slots).total * kStepWarps; }
 
+/* info word of an agent: action bits 0-5 | stat bits 6-9 (hitFriendly, hitEnemy, ateFood, reproduced) |
+ * species 10-12 | finder target + 1 in 13-23 */
 __device__ __forceinline__ uint32_t food_cell(const uint2 &f, int p)
 {
     return p < 4 ? (f.x >> (8 * p)) & 0xffu : f.y & 0xffu;
@@ -181,209 +125,233 @@ __device__ __forceinline__ uint32_t food_match(const uint2 &f, uint32_t cell)
     return m & has;
 }
 
-__global__ void step_kernel(SimDev d, int cur)
+__device__ __forceinline__ int warp_sum(int v) { return __reduce_add_sync(FULL, v); }
+
+__global__ void __launch_bounds__(kStepWarps * 32) step_kernel(SimDev d, int cur, uint32_t slots)
 {
     extern __shared__ __align__(16) unsigned char smem_raw[];
-    StepShared &sh = *reinterpret_cast<StepShared *>(smem_raw);
-    const uint32_t cap = d.cap;
-    int *accum = reinterpret_cast<int *>(smem_raw + sizeof(StepShared));
-    uint32_t *wantKey = reinterpret_cast<uint32_t *>(accum + cap);
-    uint32_t *wantMask = wantKey + cap;
-    uint32_t *ateMask = wantMask + cap / 32;
-    uint8_t *spec = reinterpret_cast<uint8_t *>(ateMask + cap / 32);
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const uint32_t w = blockIdx.x * kStepWarps + warp;
+    if (w >= d.numWorlds) return;                       /* whole warp */
+    const StepLayout L = step_layout(slots);
+    unsigned char *my = smem_raw + (size_t)L.total * warp;
+    float4 *spose = reinterpret_cast<float4 *>(my + L.pose);
+    uint2 *food = reinterpret_cast<uint2 *>(my + L.food);
+    uint32_t *chunkAgents = reinterpret_cast<uint32_t *>(my + L.chunkAgents);
+    uint32_t *chunkSpeed = reinterpret_cast<uint32_t *>(my + L.chunkSpeed);
+    int *accum = reinterpret_cast<int *>(my + L.accum);
+    int *soldrow = reinterpret_cast<int *>(my + L.oldrow);
+    uint32_t *sinfo = reinterpret_cast<uint32_t *>(my + L.info);
+    uint8_t *spec = my + L.spec;
 
-    const uint32_t w = blockIdx.x;
-    const uint32_t s = threadIdx.x;                    /* blockDim >= max(live agents, initAgents, 32) */
-    const int lane = s & 31, warp = s >> 5, nw = (blockDim.x + 31) >> 5;
+    const uint32_t cap = d.cap;
     const size_t base = (size_t)w * cap;
     const ObsSet &from = d.obs[cur];
-
-    /* ---- P0: stage the world ---- */
-    const int n0 = d.worldCount[w];
-    const int4 rb0 = d.rowBase[cur][w];
-    const bool active = (int)s < n0;
-    float4 pose = make_float4(0.f, 0.f, 1.f, 0.f);
-    int hp = 0, sp = 0, tgt = -1;
-    if (active) {
-        pose = d.pose[base + s];
-        hp = d.health[base + s];
-        sp = d.species[base + s];
-        tgt = d.target[base + s];
-    }
-    accum[s] = hp;
-    spec[s] = (uint8_t)sp;
-    if (s < cap / 32) { wantMask[s] = 0; ateMask[s] = 0; }
-    for (uint32_t c = s; c < (uint32_t)kNumChunks; c += blockDim.x) {
-        sh.chunkAgents[c] = 0;                         /* resetChunkInfoSystem (:390-396) */
-        sh.chunkSpeed[c] = 0;
-        sh.food[c] = d.food[(size_t)w * kNumChunks + c];
-    }
-    if (s < 32) {
-        const uint2 kk = d.rngKey[w];
-        const uint32_t rng0 = d.rngCount[w];
-        sh.draws[s] = key_split(Key{kk.x, kk.y}, rng0 + s);
-        if (s < 4) { sh.cnt[s] = 0; sh.hsum[s] = 0; }
-        if (s == 0) {
-            sh.rngCount = rng0;
-            sh.numFood = d.numFood[w];
-            sh.foodDirty = 0; sh.eaten = 0; sh.shots = 0;
-        }
-    }
-    /* the agent's observation row in set `cur` (rank among lower slots of its species) */
-    int tot0[4];
-    const int rank0 = block_species_rank(active ? sp - 1 : -1, tot0, sh.wcs);   /* barrier B1 */
-    int act[6] = {0, 0, 0, 0, 0, 0};
-    int oldrow = -1;
-    if (active) {
-        oldrow = comp(rb0, sp - 1) + rank0;
-        const int2 *ap = reinterpret_cast<const int2 *>(from.action + (size_t)oldrow * 6);
-        const int2 a0 = ap[0], a1 = ap[1], a2 = ap[2];
-        act[0] = a0.x; act[1] = a0.y; act[2] = a1.x; act[3] = a1.y; act[4] = a2.x; act[5] = a2.y;
-    }
-
-    /* ---- P1: addFoodSystem (thread 0) and actionSystem (every agent) ---- */
-    if (s == 0) add_food(sh);
-    uint32_t stat = 0;   /* bit0 hitFriendly, bit1 hitEnemy, bit2 ateFood, bit3 reproduced */
-    if (active) {
-        if (act[4] && tgt >= 0) {                      /* shoot with last frame's finder hit (:434-454) */
-            atomicAdd(&accum[tgt], -50);
-            atomicAdd(&sh.shots, 1u);
-            stat |= (spec[tgt] == sp) ? 1u : 2u;
-        }
-        Rot rot{pose.z, pose.w};
-        const float len = move_agent(pose.x, pose.y, rot, act[0] != 0, act[1] != 0, act[2] != 0, act[3] != 0);
-        pose.z = rot.w; pose.w = rot.z;
-        const int c = chunk_of(pose.x, pose.y);
-        atomicAdd(&sh.chunkAgents[c], 1u);
-        atomicAdd(&sh.chunkSpeed[c], (uint32_t)(len * 2.f));
-    }
-    __syncthreads();                                   /* barrier B2 */
-
-    /* ---- P2: healthSync (:505-581), speciesTrackerUpdate (:719-734) ----
-     * Common case (nobody stands on food, no slot overflow): one barrier. Breed / live flags,
-     * the any-agent-on-food vote and the warp counts for the two compaction scans all travel
-     * in one shared word per warp; the tracker sums are shared-memory atomics issued before it. */
-    const int hp0 = accum[s];
-    const int mychunk = active ? chunk_of(pose.x, pose.y) : 0;
-    const uint32_t mycell = cell_of(pose.x, pose.y);
-    const bool wants = active && food_match(sh.food[mychunk], mycell) != 0;
-    const bool canBreed = active && act[5] && tgt >= 0 && spec[tgt] == sp;
-    const int room = (int)cap - n0;                    /* makeAgent fails once the slot table is full (D1) */
     const unsigned lt = (1u << lane) - 1u;
 
-    bool breeds, live;
-    int nBreed = 0, nLive = 0, bidx = 0, lidx = 0;
-    bool ate = false;
-    for (int round = 0;; ++round) {
-        hp = hp0 + (ate ? 20 : 0);
-        breeds = canBreed && hp > 10;
-        if (breeds) hp -= 40;
-        live = active && hp > 0;
-        const unsigned bb = __ballot_sync(FULL, breeds), bl = __ballot_sync(FULL, live);
-        const unsigned bw = __ballot_sync(FULL, wants);
-        uint32_t *xch = round == 0 ? sh.xch0 : sh.xch1;
-        if (lane == 0) xch[warp] = (uint32_t)__popc(bb) | ((uint32_t)__popc(bl) << 8) | (bw && round == 0 ? 1u << 31 : 0u);
-        if (live) { atomicAdd(&sh.cnt[sp - 1], 1u); atomicAdd(&sh.hsum[sp - 1], (uint32_t)hp); }
-        if (breeds) { atomicAdd(&sh.cnt[sp - 1], 1u); atomicAdd(&sh.hsum[sp - 1], 50u); }   /* newborn, if it fits */
-        __syncthreads();                               /* barrier B3 */
-        bool anyWants = false;
-        int bbase = 0, lbase = 0;
-        nBreed = nLive = 0;
-        for (int i = 0; i < nw; ++i) {
-            const uint32_t v = xch[i];
-            const int cb = (int)(v & 0xffu), cl = (int)((v >> 8) & 0xffu);
-            if (i < warp) { bbase += cb; lbase += cl; }
-            nBreed += cb; nLive += cl;
-            anyWants |= (v >> 31) != 0;
+    /* ---- P0: stage the world: state, the action row of every agent, food; reset the chunk counters ---- */
+    /* the first 32 slots are loaded before the live count is known (slots < cap always exist): one DRAM round
+     * trip less on the critical path of nearly every world */
+    float4 pose0 = d.pose[base + lane];
+    int hp0 = d.health[base + lane];
+    uint32_t sp0 = d.species[base + lane];
+    int tgt0 = d.target[base + lane];
+    int row0 = d.row[base + lane];
+    const int n0 = d.worldCount[w];
+    const uint2 kk = d.rngKey[w];
+    const uint32_t rng0 = d.rngCount[w];
+    int numFood = d.numFood[w];
+    for (int s = lane; s < n0; s += 32) {
+        if (s >= 32) {
+            pose0 = d.pose[base + s];
+            hp0 = d.health[base + s];
+            sp0 = d.species[base + s];
+            tgt0 = d.target[base + s];
+            row0 = d.row[base + s];
         }
-        bidx = bbase + __popc(bb & lt);
-        lidx = lbase + __popc(bl & lt);
-        if (!anyWants) break;
-        /* Rare: at least one agent stands on food. Resolve in slot order so that the lowest slot
-         * wins a contested package (FoodPackage::consume CAS race, sim.inl:76-99; U11), then redo
-         * the round with the +20 applied. */
-        if (wants) {
-            wantKey[s] = ((uint32_t)mychunk << 8) | mycell;
-            atomicOr(&wantMask[s >> 5], 1u << (s & 31));
-        }
-        if (s < 4) { sh.cnt[s] = 0; sh.hsum[s] = 0; }
-        __syncthreads();
-        if (s == 0) {
-            for (uint32_t wd = 0; wd < cap / 32; ++wd) {
-                uint32_t m = wantMask[wd];
-                while (m) {
-                    const uint32_t b = (uint32_t)__ffs((int)m) - 1u;
-                    m &= m - 1u;
-                    const uint32_t slot = wd * 32 + b, key = wantKey[slot];
-                    uint2 f = sh.food[key >> 8];
-                    const uint32_t mm = food_match(f, key & 0xffu);
-                    if (mm) {
-                        const uint32_t p = (uint32_t)__ffs((int)mm) - 1u;
-                        f.y &= ~(1u << (8 + p));
-                        sh.food[key >> 8] = f;
-                        sh.numFood -= 1;
-                        sh.eaten += 1;
-                        sh.foodDirty = 1;
-                        ateMask[wd] |= 1u << b;
-                    }
-                }
+        const int2 *ap = reinterpret_cast<const int2 *>(from.action + (size_t)row0 * 6);
+        const int2 a0 = ap[0], a1 = ap[1], a2 = ap[2];
+        const uint32_t act = (a0.x != 0) | ((a0.y != 0) << 1) | ((a1.x != 0) << 2) | ((a1.y != 0) << 3) |
+                             ((a2.x != 0) << 4) | ((a2.y != 0) << 5);
+        spose[s] = pose0;
+        accum[s] = hp0;
+        soldrow[s] = row0;
+        spec[s] = (uint8_t)sp0;
+        sinfo[s] = act | (sp0 << 10) | ((uint32_t)(tgt0 + 1) << 13);
+    }
+    for (int c = lane; c < kNumChunks; c += 32) {
+        chunkAgents[c] = 0;                             /* resetChunkInfoSystem (:390-396) */
+        chunkSpeed[c] = 0;
+        food[c] = d.food[(size_t)w * kNumChunks + c];
+    }
+    __syncwarp();
+
+    /* ---- addFoodSystem + addFoodToChunk (src/sim/sim.cpp:308-387). The stream is counter-based: draw k is
+     * split_i(key, count + k) whatever happened before it. Nine steps in ten use draw 0 only; otherwise the
+     * warp pre-splits 32 draws (at most 2 + 3*7 = 23 are used), one per lane, and every lane walks the same
+     * sequential logic, fetching draw k by shuffle. ---- */
+    const Key wkey{kk.x, kk.y};
+    uint32_t foodDraws = 1;
+    bool foodDirty = false;
+    if (key_sample_i32(key_split(wkey, rng0), 0, 10) == 0) {
+        const Key mine = key_split(wkey, rng0 + (uint32_t)lane);
+        auto draw = [&](uint32_t k, int lo, int hi) {
+            return key_sample_i32(Key{__shfl_sync(FULL, mine.a, (int)k), __shfl_sync(FULL, mine.b, (int)k)}, lo, hi);
+        };
+        uint32_t k = 1;
+        uint32_t nadd = (uint32_t)draw(k++, 1, 3);
+        const uint32_t allowed = (uint32_t)kTotalAllowedFood - (uint32_t)numFood;   /* unsigned, U12 */
+        nadd = nadd < allowed ? nadd : allowed;
+        for (uint32_t i = 0; i < nadd; ++i) {
+            const uint32_t cx = (uint32_t)draw(k, 0, kChunksX);
+            const uint32_t cy = (uint32_t)draw(k + 1, 0, kChunksY);
+            k += 4;                                     /* + two discarded draws (:311-312) */
+            uint2 f = food[cx + cy * kChunksX];
+            const uint32_t mask = (f.y >> 8) & 0x1fu;
+            if (mask != 0x1fu) {
+                const uint32_t p = (uint32_t)__ffs((int)(~mask & 0x1fu)) - 1u;   /* first empty package */
+                const uint32_t rx = (uint32_t)draw(k, 0, kChunkWidth);
+                const uint32_t ry = (uint32_t)draw(k + 1, 0, kChunkWidth);
+                k += 3;                                 /* + yaw of the render-only food entity (:340) */
+                const uint32_t cell = (rx << 4) | ry;
+                if (p < 4u) f.x = (f.x & ~(0xffu << (8 * p))) | (cell << (8 * p));
+                else f.y = (f.y & ~0xffu) | cell;
+                f.y |= 1u << (8 + p);
+                __syncwarp();
+                if (lane == 0) food[cx + cy * kChunksX] = f;
+                __syncwarp();
+                numFood += 1;
+                foodDirty = true;
             }
         }
-        __syncthreads();
-        ate = active && ((ateMask[s >> 5] >> (s & 31)) & 1u);
+        foodDraws = k;
     }
-    if (ate) stat |= 4u;
-    if (breeds) stat |= 8u;
+    const uint32_t rngBase = rng0 + foodDraws;
+
+    /* ---- P1: actionSystem (:419-502) ---- */
+    for (int s = lane; s < n0; s += 32) {
+        uint32_t info = sinfo[s];
+        const int tgt = (int)((info >> 13) & 0x7ffu) - 1;
+        const uint32_t sp = (info >> 10) & 7u;
+        if ((info & 16u) && tgt >= 0) {                 /* shoot with last frame's finder hit (:434-454) */
+            atomicAdd(&accum[tgt], -50);
+            info |= (spec[tgt] == sp) ? (1u << 6) : (2u << 6);
+            info |= 1u << 24;                           /* a shot that hit (statistics) */
+        }
+        float4 pose = spose[s];
+        Rot rot{pose.z, pose.w};
+        const float len = move_agent(pose.x, pose.y, rot, (info & 1u) != 0, (info & 2u) != 0, (info & 4u) != 0, (info & 8u) != 0);
+        pose.z = rot.w; pose.w = rot.z;
+        const int c = chunk_of(pose.x, pose.y);
+        atomicAdd(&chunkAgents[c], 1u);
+        atomicAdd(&chunkSpeed[c], (uint32_t)(len * 2.f));
+        spose[s] = pose;
+        sinfo[s] = info;
+    }
+    __syncwarp();
+
+    /* ---- P2: healthSync (:505-581), updateSurroundingObservation (:583-654), speciesTrackerUpdate (:719-734),
+     * and the compaction the reference gets from SortArchetypeNode<Agent, WorldID>: survivors keep their
+     * order, then newborns in parent order (U11). Passes run in slot order. ---- */
+    const int room = (int)cap - n0;                     /* makeAgent fails once the slot table is full (D1) */
+    int nLive = 0, nBreed = 0, eaten = 0, shots = 0;
+    int cnt[4] = {0, 0, 0, 0}, hsum[4] = {0, 0, 0, 0};
+    for (int s0 = 0; s0 < n0; s0 += 32) {
+        const int s = s0 + lane;
+        const bool active = s < n0;
+        uint32_t info = 0;
+        float4 pose = make_float4(0.f, 0.f, 1.f, 0.f);
+        int hp = 0, oldrow = -1;
+        if (active) { info = sinfo[s]; pose = spose[s]; hp = accum[s]; oldrow = soldrow[s]; }
+        const int sp = (int)((info >> 10) & 7u);
+        const int tgt = (int)((info >> 13) & 0x7ffu) - 1;
+        uint32_t stat = (info >> 6) & 15u;
+        shots += __popc(__ballot_sync(FULL, (info >> 24) & 1u));
+
+        /* food: the first package of the agent's chunk at the agent's cell that still holds food. Agents that
+         * want the same cell take the matching packages in slot order (FoodPackage::consume CAS race,
+         * sim.inl:76-99 -> lowest slot wins, U11). Rare: skipped unless some agent stands on food. */
+        const int mychunk = active ? chunk_of(pose.x, pose.y) : 0;
+        const uint32_t mycell = cell_of(pose.x, pose.y);
+        const uint32_t mm = active ? food_match(food[mychunk], mycell) : 0u;
+        bool ate = false;
+        if (__any_sync(FULL, mm != 0u)) {
+            const uint32_t key = mm ? ((uint32_t)mychunk << 8) | mycell : 0x80000000u | (uint32_t)lane;
+            const unsigned group = __match_any_sync(FULL, key);
+            const int r = __popc(group & lt);           /* wanting agents of lower slot at the same cell */
+            if (mm && r < __popc(mm)) {
+                uint32_t rest = mm;
+                for (int i = 0; i < r; ++i) rest &= rest - 1u;
+                const uint32_t p = (uint32_t)__ffs((int)rest) - 1u;
+                atomicAnd(&food[mychunk].y, ~(1u << (8 + p)));
+                ate = true;
+            }
+            const int e = __popc(__ballot_sync(FULL, ate));
+            numFood -= e;
+            eaten += e;
+            foodDirty = true;
+            __syncwarp();                               /* later passes see the packages gone */
+        }
+        if (ate) { hp += 20; stat |= 4u; }
+        const bool breeds = active && (info & 32u) && tgt >= 0 && spec[tgt] == sp && hp > 10;
+        if (breeds) { hp -= 40; stat |= 8u; }
+        const bool live = active && hp > 0;
+        const unsigned bb = __ballot_sync(FULL, breeds), bl = __ballot_sync(FULL, live);
+        const int bidx = nBreed + __popc(bb & lt), lidx = nLive + __popc(bl & lt);
+        const bool childOk = breeds && bidx < room;
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            const bool mine = sp == k + 1;
+            cnt[k] += __popc(__ballot_sync(FULL, mine && live)) + __popc(__ballot_sync(FULL, mine && childOk));
+            hsum[k] += warp_sum(mine ? (live ? hp : 0) + (childOk ? 50 : 0) : 0);
+        }
+        float sn = 0.f, ss = 0.f;
+        if (live || childOk) surroundings(pose.x, pose.y, chunkAgents, chunkSpeed, sn, ss);
+        __syncwarp();                                   /* every lane has read its parked record */
+        if (live) {
+            const size_t o = base + (size_t)lidx;
+            d.pose[o] = pose;
+            d.health[o] = hp;
+            d.species[o] = (uint8_t)sp;
+            d.scratch[o] = make_float4(__int_as_float(oldrow), sn, ss, __int_as_float((int)stat));
+        }
+        if (childOk) {                                  /* park the newborn: its slot needs the final live count */
+            spose[bidx] = make_float4(pose.x, pose.y, sn, ss);
+            sinfo[bidx] = (uint32_t)sp;
+        }
+        nBreed += __popc(bb);
+        nLive += __popc(bl);
+    }
     const int bornOk = nBreed < room ? nBreed : room;
-    const bool childOk = breeds && bidx < room;
-    if (nBreed > room) {                               /* rare: take back the newborns that did not fit */
-        if (breeds && !childOk) { atomicSub(&sh.cnt[sp - 1], 1u); atomicSub(&sh.hsum[sp - 1], 50u); }
-        __syncthreads();
-    }
-
-    /* updateSurroundingObservation (:583-654); a newborn shares its parent's position */
-    float sn = 0.f, ss = 0.f;
-    if (live || childOk) surroundings(pose.x, pose.y, sh.chunkAgents, sh.chunkSpeed, sn, ss);
-
-    /* compaction: survivors keep their order, then newborns in parent order (U11) */
-    if (live) {
-        const size_t o = base + (size_t)lidx;
-        d.pose[o] = pose;
-        d.health[o] = hp;
-        d.species[o] = (uint8_t)sp;
-        d.scratch[o] = make_float4(__int_as_float(oldrow), sn, ss, __int_as_float((int)stat));
-    }
-    if (childOk) {
-        const size_t o = base + (size_t)(nLive + bidx);
-        d.pose[o] = make_float4(pose.x, pose.y, 1.f, 0.f);
+    __syncwarp();
+    for (int b = lane; b < bornOk; b += 32) {           /* a newborn shares its parent's position and surroundings */
+        const float4 c = spose[b];
+        const size_t o = base + (size_t)(nLive + b);
+        d.pose[o] = make_float4(c.x, c.y, 1.f, 0.f);
         d.health[o] = 50;
-        d.species[o] = (uint8_t)sp;
-        d.scratch[o] = make_float4(__int_as_float(-1), sn, ss, __int_as_float(0));
+        d.species[o] = (uint8_t)sinfo[b];
+        d.scratch[o] = make_float4(__int_as_float(-1), c.z, c.w, __int_as_float(0));
     }
 
     /* ---- P3: speciesInfoSync + respawn (:791-838) ---- */
     const uint32_t q = d.initAgents / kNumSpecies;
-    uint32_t c4[4], need[4], pre[4];
+    uint32_t need[4], pre[4];
     uint32_t needTotal = 0;
 #pragma unroll
     for (int k = 0; k < 4; ++k) {
-        c4[k] = sh.cnt[k];
-        need[k] = c4[k] < q ? q - c4[k] : 0u;
+        need[k] = (uint32_t)cnt[k] < q ? q - (uint32_t)cnt[k] : 0u;
         pre[k] = needTotal;
         needTotal += need[k];
     }
-    const int size1 = n0 + bornOk;                     /* table size before respawn (dead rows still count) */
+    const int size1 = n0 + bornOk;                      /* table size before respawn (dead rows still count) */
     const int room2 = (int)cap - size1;
     const uint32_t respOk = (int)needTotal < room2 ? needTotal : (uint32_t)room2;
-    const uint32_t rngBase = sh.rngCount;
-    if (s < needTotal) {
+    for (uint32_t s = (uint32_t)lane; s < needTotal; s += 32u) {
         int k = 0;
         if (s >= pre[1] + need[1]) k = (s >= pre[2] + need[2]) ? 3 : 2;
         else if (s >= pre[0] + need[0]) k = 1;
-        const uint2 kk = d.rngKey[w];
-        const Key key{kk.x, kk.y};
-        const float x = key_sample_uniform(key_split(key, rngBase + 2u * s)) * kWorldX;
-        const float y = key_sample_uniform(key_split(key, rngBase + 2u * s + 1u)) * kWorldY;
+        const float x = key_sample_uniform(key_split(wkey, rngBase + 2u * s)) * kWorldX;
+        const float y = key_sample_uniform(key_split(wkey, rngBase + 2u * s + 1u)) * kWorldY;
         if (s < respOk) {
             const size_t o = base + (size_t)(nLive + bornOk) + s;
             d.pose[o] = make_float4(x, y, 1.f, 0.f);
@@ -392,7 +360,7 @@ __global__ void step_kernel(SimDev d, int cur)
             d.scratch[o] = make_float4(__int_as_float(-1), 0.f, 0.f, __int_as_float(0));
         }
     }
-    if (s == 0) {
+    if (lane == 0) {
         int4 liveRows;
         int *lr = &liveRows.x;
         float4 rw;
@@ -400,17 +368,17 @@ __global__ void step_kernel(SimDev d, int cur)
 #pragma unroll
         for (int k = 0; k < 4; ++k) {
             const uint32_t ok = respOk > pre[k] ? (respOk - pre[k] < need[k] ? respOk - pre[k] : need[k]) : 0u;
-            lr[k] = (int)(c4[k] + ok);
-            rwp[k] = species_reward(c4[k], sh.hsum[k], d.initAgents);
+            lr[k] = cnt[k] + (int)ok;
+            rwp[k] = species_reward((uint32_t)cnt[k], (uint32_t)hsum[k], d.initAgents);
         }
         const int count1 = nLive + bornOk + (int)respOk;
         d.speciesLive[w] = liveRows;
-        d.speciesCount[w] = make_int4((int)c4[0], (int)c4[1], (int)c4[2], (int)c4[3]);
-        d.speciesHealth[w] = make_int4((int)sh.hsum[0], (int)sh.hsum[1], (int)sh.hsum[2], (int)sh.hsum[3]);
+        d.speciesCount[w] = make_int4(cnt[0], cnt[1], cnt[2], cnt[3]);
+        d.speciesHealth[w] = make_int4(hsum[0], hsum[1], hsum[2], hsum[3]);
         d.speciesReward[w] = rw;
         d.worldCount[w] = count1;
         d.rngCount[w] = rngBase + 2u * needTotal;
-        d.numFood[w] = sh.numFood;
+        d.numFood[w] = numFood;
         /* partial sums of the row scan: one tile = kScanTile consecutive worlds */
         TileSum *ts = d.tileSum[cur] + (w / kScanTile);
 #pragma unroll
@@ -418,15 +386,19 @@ __global__ void step_kernel(SimDev d, int cur)
         atomicMax(&ts->maxCount, count1);
         const uint32_t deaths = (uint32_t)(n0 - nLive);
         const uint32_t overflow = (uint32_t)(nBreed - bornOk) + (needTotal - respOk);
-        if (bornOk | (int)deaths | (int)respOk | (int)overflow | (int)sh.eaten | (int)sh.shots) {
-            WorldStats ws = d.wstats[w];
-            ws.births += (uint32_t)bornOk; ws.deaths += deaths; ws.respawns += respOk;
-            ws.overflow += overflow; ws.eaten += sh.eaten; ws.shots += sh.shots;
-            d.wstats[w] = ws;
-        }
+        /* cumulative event counters: fire-and-forget reductions, nothing waits on them */
+        WorldStats *ws = d.wstats + w;
+        if (bornOk) atomicAdd(&ws->births, (uint32_t)bornOk);
+        if (deaths) atomicAdd(&ws->deaths, deaths);
+        if (respOk) atomicAdd(&ws->respawns, respOk);
+        if (overflow) atomicAdd(&ws->overflow, overflow);
+        if (eaten) atomicAdd(&ws->eaten, (uint32_t)eaten);
+        if (shots) atomicAdd(&ws->shots, (uint32_t)shots);
     }
-    if (sh.foodDirty)
-        for (uint32_t c = s; c < (uint32_t)kNumChunks; c += blockDim.x) d.food[(size_t)w * kNumChunks + c] = sh.food[c];
+    if (foodDirty) {
+        __syncwarp();
+        for (int c = lane; c < kNumChunks; c += 32) d.food[(size_t)w * kNumChunks + c] = food[c];
+    }
 }
 
 /* ------------------------------------------------------------------------- */
@@ -696,6 +668,7 @@ __device__ __forceinline__ void export_world(const SimDev &d, int cur, int with_
             const float sterm = sp == 1 ? srew.x : sp == 2 ? srew.y : sp == 3 ? srew.z : srew.w;
             to.reward[row] = with_sensors ? agent_reward(sterm, hp, (st & 4u) != 0, (st & 8u) != 0, (st & 2u) != 0) : 0.f;
             d.sensorIndex[off + s] = row;
+            d.row[base + s] = row;
             if (!with_sensors) d.target[base + s] = (int16_t)-1;
             reinterpret_cast<int4 *>(to.prev_stats)[row] = pst;
             reinterpret_cast<float2 *>(to.prev_position)[row] = ppos;
@@ -961,11 +934,14 @@ void launch_init(const SimDev &d, cudaStream_t s)
     init_kernel<<<d.numWorlds, threads, 0, s>>>(d);
 }
 
-void launch_step(const SimDev &d, int cur, uint32_t threads, cudaStream_t s)
+void launch_step(const SimDev &d, int cur, uint32_t slots, cudaStream_t s)
 {
-    /* threads: a multiple of 32 that covers every live slot and the respawn draws; cap always does */
-    if (threads == 0 || threads > d.cap) threads = d.cap;
-    step_kernel<<<d.numWorlds, threads, step_smem_bytes(d.cap), s>>>(d, cur);
+    /* slots: a bound on the live agents of any world before the step; the capacity always is one */
+    if (slots == 0 || slots > d.cap) slots = d.cap;
+    const size_t smem = step_smem_bytes(slots);
+    if (smem > 48 * 1024)
+        cudaFuncSetAttribute(step_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    step_kernel<<<(d.numWorlds + kStepWarps - 1) / kStepWarps, kStepWarps * 32, smem, s>>>(d, cur, slots);
 }
 
 void launch_scan(const SimDev &d, int cur, int count_step, cudaStream_t s)
