@@ -534,7 +534,7 @@ template <> struct Sense<false> {
 
 /* per-warp shared memory: agent arrays sized for `slots` agents + the keys of one sensor tile */
 struct ExportLayout {
-    uint32_t best, pos, head, queue, pairq, newrow, oldrow, theta, spec, total;
+    uint32_t best, pos, head, queue, pairq, candq, newrow, oldrow, theta, spec, total;
 };
 __host__ __device__ inline ExportLayout export_layout(uint32_t slots, uint32_t tile, uint32_t key_bytes)
 {
@@ -545,6 +545,7 @@ __host__ __device__ inline ExportLayout export_layout(uint32_t slots, uint32_t t
     L.head = o; o += slots * 8;                         /* float2 unit heading (cull only) */
     L.queue = o; o += kQueue * 4;
     L.pairq = o; o += kQueue * 4;
+    L.candq = o; o += kQueue * 4;
     L.newrow = o; o += slots * 4;
     L.oldrow = o; o += slots * 4;
     L.theta = o; o += slots * 4;
@@ -604,6 +605,7 @@ __device__ __forceinline__ void export_world(const SimDev &d, int cur, int with_
     float2 *head = reinterpret_cast<float2 *>(my + L.head);
     uint32_t *queue = reinterpret_cast<uint32_t *>(my + L.queue);
     uint32_t *pairq = reinterpret_cast<uint32_t *>(my + L.pairq);
+    uint32_t *candq = reinterpret_cast<uint32_t *>(my + L.candq);
     int *newrow = reinterpret_cast<int *>(my + L.newrow);
     int *oldrow = reinterpret_cast<int *>(my + L.oldrow);
     float *theta = reinterpret_cast<float *>(my + L.theta);
@@ -713,20 +715,29 @@ __device__ __forceinline__ void export_world(const SimDev &d, int cur, int with_
         __syncwarp();
 
         int qn = 0;                                     /* pending tests, warp-uniform, < 32 between chunks */
+        auto test = [&](int ol, int j, int r) {
+            const float2 qi = pos[tile0 + ol], qj = pos[j];
+            const Ray ray = make_ray(theta[tile0 + ol], r);
+            float t;
+            if (ray_sphere(ray, qi.x - qj.x, qi.y - qj.y, t) && t > kNearSphere)
+                atomicMin(&best[ol * kSensor + r], S::make(t, j));
+        };
         auto run_tests = [&](int first, int count) {
             if (lane < count) {
                 const uint32_t e = queue[first + lane];
-                const int r = (int)(e & 31u), j = (int)((e >> 5) & ((1u << JB) - 1u)), ol = (int)(e >> (5 + JB));
-                const float2 qi = pos[tile0 + ol], qj = pos[j];
-                const Ray ray = make_ray(theta[tile0 + ol], r);
-                float t;
-                if (ray_sphere(ray, qi.x - qj.x, qi.y - qj.y, t) && t > kNearSphere)
-                    atomicMin(&best[ol * kSensor + r], S::make(t, j));
+                test((int)(e >> (5 + JB)), (int)((e >> 5) & ((1u << JB) - 1u)), (int)(e & 31u));
             }
         };
-        /* `flush`: also run a last partial chunk of tests */
+        /* 32 pairs with candidates, one per lane. The first candidate of every pair is tested right here, at full
+         * lane occupancy and with no queue traffic (most pairs have exactly one); the others are expanded into
+         * the test queue. `flush`: also run a last partial chunk of queued tests. */
         auto expand = [&](uint32_t info, bool valid, bool flush) {
-            const int c = valid ? (int)((info >> 5) & 31u) + (int)((info >> 13) & 15u) : 0;
+            if (valid) {
+                const int cf = (int)((info >> 5) & 31u);
+                test((int)(info >> (17 + JB)), (int)((info >> 17) & ((1u << JB) - 1u)),
+                     cf > 0 ? (int)(info & 31u) : kFwdRays + (int)((info >> 10) & 7u));
+            }
+            const int c = valid ? (int)((info >> 5) & 31u) + (int)((info >> 13) & 15u) - 1 : 0;
             int inc = c;
 #pragma unroll
             for (int o = 1; o < 32; o <<= 1) {
@@ -744,7 +755,7 @@ __device__ __forceinline__ void export_world(const SimDev &d, int cur, int with_
                     if (v <= q) own += st;
                 }
                 const uint32_t oi = __shfl_sync(FULL, info, own);
-                const int k = q - __shfl_sync(FULL, exc, own);
+                const int k = q - __shfl_sync(FULL, exc, own) + 1;   /* candidate 0 was tested above */
                 const int ocf = (int)((oi >> 5) & 31u);
                 const int r = k < ocf ? (int)(oi & 31u) + k : kFwdRays - ocf + (int)((oi >> 10) & 7u) + k;
                 if (q < total) queue[qn + lane] = ((oi >> 17) << 5) | (uint32_t)r;
@@ -760,7 +771,28 @@ __device__ __forceinline__ void export_world(const SimDev &d, int cur, int with_
             }
         };
 
-        int pqn = 0;                                    /* pending pairs, warp-uniform, < 32 between iterations */
+        int pqn = 0;                                    /* pending pairs with candidates, warp-uniform, < 32 between calls */
+        /* stage 2 of the cull: 32 pairs that passed the wedge test, one per lane -> candidate spans */
+        auto spans = [&](uint32_t code, bool valid) {
+            const int ol = (int)(code >> JB), j = (int)(code & ((1u << JB) - 1u));
+            const float2 pi = pos[tile0 + ol], hd = head[tile0 + ol], pj = pos[j];
+            const RayCount rc = pair_spans(pi.x - pj.x, pi.y - pj.y, Dir{hd.x, hd.y});
+            /* flo 0-4 | cf 5-9 | blo 10-12 | cb 13-16 | target 17.. (JB bits) | observer of the tile */
+            const uint32_t info = (uint32_t)(rc.flo & 31) | ((uint32_t)rc.cf << 5) | ((uint32_t)(rc.blo & 7) << 10) |
+                                  ((uint32_t)rc.cb << 13) | (code << 17);
+            const bool has = valid && (rc.cf + rc.cb) > 0;
+            const unsigned bal = __ballot_sync(FULL, has);
+            if (has) pairq[pqn + __popc(bal & lt)] = info;
+            pqn += __popc(bal);
+            __syncwarp();
+            if (pqn >= 32) {
+                pqn -= 32;
+                expand(pairq[pqn + lane], true, false);
+                __syncwarp();
+            }
+        };
+
+        int cqn = 0;                                    /* pairs that passed stage 1, warp-uniform, < 32 between iterations */
         for (int sub0 = 0; sub0 < m; sub0 += 32) {
             const int ms = min(32, m - sub0);
             const int lg = ms > 16 ? 5 : ms > 8 ? 4 : ms > 4 ? 3 : ms > 2 ? 2 : ms > 1 ? 1 : 0;   /* 1 << lg >= ms */
@@ -768,25 +800,24 @@ __device__ __forceinline__ void export_world(const SimDev &d, int cur, int with_
             const bool on_i = il < ms;
             const int ol = sub0 + (on_i ? il : 0);      /* observer within the tile */
             const float2 pi = pos[tile0 + ol], hd = head[tile0 + ol];
+            const int jend = on_i ? n : 0;
             for (int j0 = 0; j0 < n; j0 += tpi) {
                 const int j = j0 + jl;
                 const float2 pj = pos[min(j, n - 1)];
-                const RayCount rc = pair_spans(pi.x - pj.x, pi.y - pj.y, Dir{hd.x, hd.y});
-                /* flo 0-4 | cf 5-9 | blo 10-12 | cb 13-16 | target 17.. (JB bits) | observer of the tile */
-                const uint32_t info = (uint32_t)(rc.flo & 31) | ((uint32_t)rc.cf << 5) | ((uint32_t)(rc.blo & 7) << 10) |
-                                      ((uint32_t)rc.cb << 13) | ((uint32_t)j << 17) | ((uint32_t)ol << (17 + JB));
-                const bool has = on_i && j < n && (rc.cf + rc.cb) > 0;
-                const unsigned bal = __ballot_sync(FULL, has);
-                if (has) pairq[pqn + __popc(bal & lt)] = info;
-                pqn += __popc(bal);
-                if (pqn >= 32) {
+                /* stage 1: is the target anywhere near the two fans? (pair_maybe, sim_prims.cuh) */
+                const bool maybe = pair_maybe(pi.x - pj.x, pi.y - pj.y, Dir{hd.x, hd.y}) && j < jend;
+                const unsigned bal = __ballot_sync(FULL, maybe);
+                if (maybe) candq[cqn + __popc(bal & lt)] = ((uint32_t)ol << JB) | (uint32_t)j;
+                cqn += __popc(bal);
+                if (cqn >= 32) {
                     __syncwarp();
-                    pqn -= 32;
-                    expand(pairq[pqn + lane], true, false);
+                    cqn -= 32;
+                    spans(candq[cqn + lane], true);
                 }
             }
         }
         __syncwarp();
+        spans(lane < cqn ? candq[lane] : 0u, lane < cqn);
         expand(lane < pqn ? pairq[lane] : 0u, lane < pqn, true);
 
         for (int idx = lane; idx < m * 8; idx += 32) {

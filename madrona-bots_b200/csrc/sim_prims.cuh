@@ -375,8 +375,24 @@ MBP_HD RayCount pair_spans(float ocx, float ocy, Dir h)
     return rc;
 }
 
+/* First, cheap stage of the cull: can the pair have candidates at all? Both fans together cover the double
+ * wedge |left| <= |along| around the heading axis. With psi the angle between the target direction and that
+ * axis, pair_spans() yields candidates only when psi <= pi/4 + half, and
+ *   |left| - |along| = D * sqrt(2) * sin(psi - pi/4)  <=  D * sqrt(2) * sin(half)  <  1.54
+ * for every D in [1.095, 200] (half >= pi/4 only below D = 1.47, where |left| - |along| <= D anyway). Half of
+ * all pairs fail this and never reach pair_spans(). */
+constexpr float kCullWedgeSlack = 1.6f;
+
+MBP_HD bool pair_maybe(float ocx, float ocy, Dir h)
+{
+    const float al = mb_fmaf(ocx, h.x, ocy * h.y);
+    const float lf = mb_fmaf(ocx, h.y, -(ocy * h.x));
+    return fabsf(lf) - fabsf(al) <= kCullWedgeSlack;
+}
+
 MBP_HD bool pair_candidates(float ocx, float ocy, Dir h, RaySpan &sp)
 {
+    if (!pair_maybe(ocx, ocy, h)) { sp.flo = sp.blo = 0; sp.fhi = sp.bhi = -1; return false; }
     const RayCount rc = pair_spans(ocx, ocy, h);
     sp.flo = rc.flo; sp.fhi = rc.flo + rc.cf - 1;
     sp.blo = rc.blo; sp.bhi = rc.blo + rc.cb - 1;

@@ -41,5 +41,7 @@ def shim():
     L.shim_cull_trials.argtypes = [ctypes.c_uint64, ctypes.c_int, ctypes.c_int, ctypes.c_int,
                                    ctypes.POINTER(ctypes.c_longlong)]
     L.shim_cull_trials.restype = ctypes.c_longlong
+    L.shim_wedge_trials.argtypes = [ctypes.c_uint64, ctypes.c_longlong, ctypes.POINTER(ctypes.c_longlong)]
+    L.shim_wedge_trials.restype = ctypes.c_longlong
     _lib = L
     return L

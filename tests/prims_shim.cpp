@@ -125,4 +125,36 @@ long long shim_cull_trials(uint64_t seed, int trials, int n, int mode, long long
     return bad;
 }
 
+/* pair_maybe (stage 1 of the cull) must pass every pair for which pair_spans reports candidates. Random pairs
+ * over the whole world plus pairs placed next to the wedge edges at every distance. Returns violations;
+ * *passed = pairs that survive stage 1. */
+long long shim_wedge_trials(uint64_t seed, long long trials, long long *passed)
+{
+    uint64_t s = seed * 2654435761ull + 99ull;
+    long long bad = 0;
+    *passed = 0;
+    for (long long tr = 0; tr < trials; ++tr) {
+        const float ang = (urand(s) * 2.f - 1.f) * kPi * 0.5f;
+        const float nrm = 1.f + (urand(s) - 0.5f) * 2e-3f;
+        const Rot rot{cosf(ang) * nrm, sinf(ang) * nrm};
+        const Dir h = cull_heading(rot);
+        float ocx, ocy;
+        if (tr & 1) {
+            ocx = (urand(s) * 2.f - 1.f) * 127.f; ocy = (urand(s) * 2.f - 1.f) * 95.f;
+        } else {
+            /* near a wedge edge: direction heading +- pi/4 (+ pi), offset sideways by about one radius */
+            const float dist = 1.0f + urand(s) * urand(s) * 160.f;
+            const float edge = atan2f(h.y, h.x) + kPi * 0.25f * (float)(1 + 2 * (int)(lcg(s) & 3u));
+            const float off = (urand(s) * 2.f - 1.f) * 1.7f;
+            ocx = -(cosf(edge) * dist - sinf(edge) * off);
+            ocy = -(sinf(edge) * dist + cosf(edge) * off);
+        }
+        const RayCount rc = pair_spans(ocx, ocy, h);
+        const bool maybe = pair_maybe(ocx, ocy, h);
+        if (maybe) ++*passed;
+        if ((rc.cf + rc.cb) > 0 && !maybe) ++bad;
+    }
+    return bad;
+}
+
 } /* extern "C" */

@@ -148,3 +148,12 @@ def test_culled_sensor_equals_exhaustive(S, mode, n, trials):
     assert per_pair < 32          # the cull must actually cull
     if mode == 0 and n == 33:
         assert per_pair < 0.6, per_pair
+
+
+def test_wedge_stage_never_rejects_a_pair_with_candidates(S):
+    """Stage 1 of the cull (pair_maybe) is conservative w.r.t. stage 2 (pair_spans), and rejects about half of
+    uniformly random pairs."""
+    passed = ctypes.c_longlong()
+    n = 4_000_000
+    assert S.shim_wedge_trials(77, n, ctypes.byref(passed)) == 0
+    assert passed.value < 0.85 * n
