@@ -164,6 +164,17 @@ int mbots_launch_count(mbots_sim *sim, uint64_t *out);
 int mbots_profile(mbots_sim *sim, int32_t enable);
 int mbots_profile_read(mbots_sim *sim, float out_ms[4], uint32_t out_calls[4]);
 
+/* Simulator state checkpoint / restore. The reference has no such facility (its
+ * learn/ckpt.py saves network weights only); this is SURVEY section 8(f) item 3: dump / reload every
+ * persistent array of the handle (agent SoA, food, RNG keys + draw counters, observation rows, episode
+ * counters) so that a rollout can be replayed bit-exactly from any step. The blob is host memory owned
+ * by the caller; mbots_state_bytes gives its size for the CURRENT population. Restoring requires a
+ * handle created with the same num_worlds, capacity and init_num_agents_per_world (MBOTS_EINVAL
+ * otherwise). All three synchronise the stream; MBOTS_ESTATE while asynchronous steps are pending. */
+int mbots_state_bytes(mbots_sim *sim, uint64_t *out);
+int mbots_save_state(mbots_sim *sim, void *host, uint64_t bytes, void *stream);
+int mbots_load_state(mbots_sim *sim, const void *host, uint64_t bytes, void *stream);
+
 const char *mbots_last_error(void);
 const char *mbots_version(void);
 

@@ -478,3 +478,123 @@ const char *mbots_last_error(void) { return g_err.c_str(); }
 const char *mbots_version(void) { return "mbots-b200 0.1 (sm_100a)"; }
 
 } /* extern "C" */
+
+/* ---- simulator state checkpoint / restore (the reference has none) ------------
+ * A checkpoint is a self-describing byte blob: header, then every persistent array of the handle. Agent
+ * state travels whole (numWorlds x capacity slots), observation rows are cut at the live row count, and
+ * the blob is always written as if obs set 0 were current, so a restore lands in a fixed configuration. */
+namespace {
+
+struct CkptHeader {
+    char magic[8];                 /* "MBOTSCK1" */
+    uint32_t numWorlds, cap, initAgents, worldIdOffset, seed, totalAgents;
+    uint64_t bytes;                /* whole blob */
+    Totals totals;
+};
+
+struct Segment { void *ptr; size_t bytes; };
+
+/* the persistent arrays, in blob order; `set` = obs set to read from / write to */
+void ckpt_segments(mbots_sim *s, int set, size_t A, std::vector<Segment> &out)
+{
+    SimDev &d = s->d;
+    const size_t W = d.numWorlds, slots = W * d.cap;
+    auto add = [&](void *p, size_t b) { out.push_back(Segment{p, b}); };
+    add(d.pose, slots * 16); add(d.health, slots * 4); add(d.species, slots); add(d.target, slots * 2);
+    add(d.scratch, slots * 16); add(d.row, slots * 4);
+    add(d.worldCount, W * 4); add(d.worldOffset, W * 4); add(d.rngKey, W * 8); add(d.rngCount, W * 4);
+    add(d.numFood, W * 4); add(d.food, W * 48 * 8); add(d.speciesLive, W * 16); add(d.rowBase[set], W * 16);
+    add(d.speciesCount, W * 16); add(d.speciesReward, W * 16); add(d.speciesHealth, W * 16);
+    add(d.wstats, W * sizeof(WorldStats));
+    add(d.sensorIndex, A * 4);
+    ObsSet &o = d.obs[set];
+    add(o.action, A * 24); add(o.prev_action, A * 24); add(o.hidden, A * 64); add(o.prev_hidden, A * 64);
+    add(o.reward, A * 4); add(o.prev_reward, A * 4); add(o.position, A * 8); add(o.prev_position, A * 8);
+    add(o.health, A * 4); add(o.prev_health, A * 4); add(o.surrounding, A * 8); add(o.prev_surrounding, A * 8);
+    add(o.stats, A * 16); add(o.prev_stats, A * 16); add(o.semantic, A * 32); add(o.prev_semantic, A * 32);
+    add(o.depth, A * 32); add(o.prev_depth, A * 32);
+}
+
+uint64_t ckpt_total(const std::vector<Segment> &segs)
+{
+    uint64_t b = sizeof(CkptHeader);
+    for (const Segment &g : segs) b += (g.bytes + 15u) & ~(uint64_t)15u;
+    return b;
+}
+
+} // namespace
+
+extern "C" {
+
+int mbots_state_bytes(mbots_sim *s, uint64_t *out)
+{
+    if (!s || !out) return fail(MBOTS_EINVAL, "null argument");
+    if (s->dirty) return fail(MBOTS_ESTATE, "asynchronous work pending: call mbots_sync first");
+    std::vector<Segment> segs;
+    ckpt_segments(s, s->cur, s->totalAgents, segs);
+    *out = ckpt_total(segs);
+    return MBOTS_OK;
+}
+
+int mbots_save_state(mbots_sim *s, void *host, uint64_t bytes, void *stream)
+{
+    if (!s || !host) return fail(MBOTS_EINVAL, "null argument");
+    if (s->dirty) return fail(MBOTS_ESTATE, "asynchronous work pending: call mbots_sync first");
+    std::vector<Segment> segs;
+    ckpt_segments(s, s->cur, s->totalAgents, segs);
+    const uint64_t need = ckpt_total(segs);
+    if (bytes < need) return fail(MBOTS_EINVAL, "buffer smaller than mbots_state_bytes()");
+    DeviceGuard g(s->device);
+    cudaStream_t st = (cudaStream_t)stream;
+    CkptHeader h;
+    memset(&h, 0, sizeof h);
+    memcpy(h.magic, "MBOTSCK1", 8);
+    h.numWorlds = s->d.numWorlds; h.cap = s->d.cap; h.initAgents = s->d.initAgents;
+    h.worldIdOffset = s->d.worldIdOffset; h.seed = s->d.seed; h.totalAgents = s->totalAgents;
+    h.bytes = need;
+    CU(cudaMemcpyAsync(&h.totals, s->d.totals, sizeof(Totals), cudaMemcpyDeviceToHost, st));
+    unsigned char *p = static_cast<unsigned char *>(host) + sizeof(CkptHeader);
+    for (const Segment &sg : segs) {
+        if (sg.bytes) CU(cudaMemcpyAsync(p, sg.ptr, sg.bytes, cudaMemcpyDeviceToHost, st));
+        p += (sg.bytes + 15u) & ~(size_t)15u;
+    }
+    CU(cudaStreamSynchronize(st));
+    memcpy(host, &h, sizeof h);
+    return MBOTS_OK;
+}
+
+int mbots_load_state(mbots_sim *s, const void *host, uint64_t bytes, void *stream)
+{
+    if (!s || !host) return fail(MBOTS_EINVAL, "null argument");
+    if (bytes < sizeof(CkptHeader)) return fail(MBOTS_EINVAL, "not a checkpoint (too short)");
+    CkptHeader h;
+    memcpy(&h, host, sizeof h);
+    if (memcmp(h.magic, "MBOTSCK1", 8) != 0) return fail(MBOTS_EINVAL, "not a checkpoint (bad magic)");
+    if (h.numWorlds != s->d.numWorlds || h.cap != s->d.cap || h.initAgents != s->d.initAgents)
+        return fail(MBOTS_EINVAL, "checkpoint was taken with a different num_worlds / capacity / init agents");
+    if ((uint64_t)h.totalAgents > (uint64_t)s->d.numWorlds * s->d.cap) return fail(MBOTS_EINVAL, "corrupt checkpoint");
+    DeviceGuard g(s->device);
+    cudaStream_t st = (cudaStream_t)stream;
+    CU(cudaStreamSynchronize(st));
+    std::vector<Segment> segs;
+    ckpt_segments(s, 0, h.totalAgents, segs);
+    if (ckpt_total(segs) != h.bytes || bytes < h.bytes) return fail(MBOTS_EINVAL, "checkpoint size mismatch");
+    const unsigned char *p = static_cast<const unsigned char *>(host) + sizeof(CkptHeader);
+    for (const Segment &sg : segs) {
+        if (sg.bytes) CU(cudaMemcpyAsync(sg.ptr, p, sg.bytes, cudaMemcpyHostToDevice, st));
+        p += (sg.bytes + 15u) & ~(size_t)15u;
+    }
+    const size_t tiles = (s->d.numWorlds + kScanTile - 1) / kScanTile;
+    CU(cudaMemsetAsync(s->d.tileSum[0], 0, tiles * sizeof(TileSum), st));
+    CU(cudaMemsetAsync(s->d.tileSum[1], 0, tiles * sizeof(TileSum), st));
+    CU(cudaMemcpyAsync(s->d.totals, &h.totals, sizeof(Totals), cudaMemcpyHostToDevice, st));
+    CU(cudaStreamSynchronize(st));
+    s->d.worldIdOffset = h.worldIdOffset; s->d.seed = h.seed;
+    s->cur = 0;
+    *s->hTotals = h.totals;
+    s->totalAgents = h.totalAgents;
+    s->dirty = false;
+    return MBOTS_OK;
+}
+
+} /* extern "C" */

@@ -193,6 +193,28 @@ class SimManager:
         _native.check(self._lib.mbots_copy_to_host(self._h, EXPORT[name], ctypes.c_void_p(host_ptr), nbytes,
                                                    self._stream()), "mbots_copy_to_host")
 
+    # ---- state checkpoint / restore ---------------------------
+    def save_state(self, path=None):
+        """Every persistent array of the simulator as one uint8 numpy blob (also written to `path`
+        when given). `load_state` of that blob into a handle of the same shape resumes the rollout
+        bit-exactly."""
+        import numpy as np
+        n = ctypes.c_uint64()
+        _native.check(self._lib.mbots_state_bytes(self._h, ctypes.byref(n)), "mbots_state_bytes")
+        blob = np.empty(n.value, dtype=np.uint8)
+        _native.check(self._lib.mbots_save_state(self._h, ctypes.c_void_p(blob.ctypes.data), n.value,
+                                                 self._stream()), "mbots_save_state")
+        if path is not None:
+            blob.tofile(path)
+        return blob
+
+    def load_state(self, blob_or_path):
+        import numpy as np
+        blob = np.fromfile(blob_or_path, dtype=np.uint8) if isinstance(blob_or_path, (str, bytes)) or \
+            hasattr(blob_or_path, "__fspath__") else np.ascontiguousarray(blob_or_path, dtype=np.uint8)
+        _native.check(self._lib.mbots_load_state(self._h, ctypes.c_void_p(blob.ctypes.data), blob.nbytes,
+                                                 self._stream()), "mbots_load_state")
+
 
 class ScriptBotsViewer:
     """The reference's Vulkan viewer (src/gfx, src/entry/entry.cpp:46-80). Unavailable on this
