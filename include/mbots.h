@@ -135,6 +135,11 @@ int mbots_num_agents(mbots_sim *sim, uint32_t *out);
  * pointer, dims and dtype of one export. `id` is an mbots_export_id. */
 int mbots_tensor(mbots_sim *sim, int32_t id, void **dev_ptr, int64_t dims[2], int32_t *dtype);
 
+/* Rows every agent-indexed export is allocated for (num_worlds x per-world capacity): the buffers behind
+ * mbots_tensor() stay valid, at fixed addresses, for this many rows, so a binding may build one view per
+ * export and re-slice it to the live count after each step instead of re-wrapping the pointer. */
+int mbots_row_capacity(mbots_sim *sim, uint64_t *out);
+
 /* Manager::setAction (src/entry/mgr.cpp:251-272): write one row of the action export. */
 int mbots_set_action(mbots_sim *sim, uint32_t agent_idx, int32_t forward, int32_t backward,
                      int32_t rotate_left, int32_t rotate_right, int32_t shoot, int32_t breed);

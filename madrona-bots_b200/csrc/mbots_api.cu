@@ -47,6 +47,7 @@ struct mbots_sim {
     /* per-kernel timing */
     bool profile;
     cudaEvent_t ev[5], evShift[2];
+    bool shiftPending;             /* evShift recorded, elapsed time not read yet */
     double ms[K_COUNT];
     uint32_t calls[K_COUNT];
 };
@@ -132,9 +133,22 @@ void free_all(mbots_sim *s)
     for (auto &e : s->evShift) if (e) cudaEventDestroy(e);
 }
 
+/* the shift kernel's events are read lazily so that profiling does not make the asynchronous shift blocking */
+void resolve_shift_timing(mbots_sim *s)
+{
+    if (!s->shiftPending) return;
+    s->shiftPending = false;
+    float a = 0;
+    if (cudaEventSynchronize(s->evShift[1]) == cudaSuccess &&
+        cudaEventElapsedTime(&a, s->evShift[0], s->evShift[1]) == cudaSuccess) {
+        s->ms[K_SHIFT] += a; s->calls[K_SHIFT]++;
+    }
+}
+
 int finish(mbots_sim *s, cudaStream_t st)
 {
     CU(cudaStreamSynchronize(st));
+    resolve_shift_timing(s);
     s->totalAgents = s->hTotals->totalAgents;
     s->dirty = false;
     return MBOTS_OK;
@@ -294,16 +308,10 @@ int mbots_shift_observations_async(mbots_sim *s, void *stream)
     if (!s) return fail(MBOTS_EINVAL, "null handle");
     DeviceGuard g(s->device);
     cudaStream_t st = (cudaStream_t)stream;
-    if (s->profile) cudaEventRecord(s->evShift[0], st);
+    if (s->profile) { resolve_shift_timing(s); cudaEventRecord(s->evShift[0], st); }
     /* grid sized from the capacity bound when the host count is stale */
     launch_shift(s->d, s->cur, s->dirty ? s->d.numWorlds * s->d.cap : s->totalAgents, st);
-    if (s->profile) {
-        cudaEventRecord(s->evShift[1], st);
-        CU(cudaEventSynchronize(s->evShift[1]));
-        float a = 0;
-        cudaEventElapsedTime(&a, s->evShift[0], s->evShift[1]);
-        s->ms[K_SHIFT] += a; s->calls[K_SHIFT]++;
-    }
+    if (s->profile) { cudaEventRecord(s->evShift[1], st); s->shiftPending = true; }
     CU(cudaGetLastError());
     s->launches += 1;
     return MBOTS_OK;
@@ -322,6 +330,13 @@ int mbots_num_agents(mbots_sim *s, uint32_t *out)
 {
     if (!s || !out) return fail(MBOTS_EINVAL, "null argument");
     *out = s->totalAgents;
+    return MBOTS_OK;
+}
+
+int mbots_row_capacity(mbots_sim *s, uint64_t *out)
+{
+    if (!s || !out) return fail(MBOTS_EINVAL, "null argument");
+    *out = (uint64_t)s->d.numWorlds * s->d.cap;
     return MBOTS_OK;
 }
 
@@ -459,6 +474,7 @@ int mbots_launch_count(mbots_sim *s, uint64_t *out)
 int mbots_profile(mbots_sim *s, int32_t enable)
 {
     if (!s) return fail(MBOTS_EINVAL, "null handle");
+    resolve_shift_timing(s);
     s->profile = enable != 0;
     for (int i = 0; i < K_COUNT; ++i) { s->ms[i] = 0; s->calls[i] = 0; }
     return MBOTS_OK;
@@ -467,6 +483,7 @@ int mbots_profile(mbots_sim *s, int32_t enable)
 int mbots_profile_read(mbots_sim *s, float out_ms[4], uint32_t out_calls[4])
 {
     if (!s || !out_ms || !out_calls) return fail(MBOTS_EINVAL, "null argument");
+    resolve_shift_timing(s);
     for (int i = 0; i < K_COUNT; ++i) {
         out_calls[i] = s->calls[i];
         out_ms[i] = s->calls[i] ? (float)(s->ms[i] / s->calls[i]) : 0.f;

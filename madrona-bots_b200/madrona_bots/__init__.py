@@ -27,7 +27,8 @@ class Tensor:
     """madrona.Tensor look-alike (M/src/python/bindings.cpp:52-68): a typed, shaped device
     pointer with `to_torch()` returning a zero-copy view on the simulator's GPU."""
 
-    def __init__(self, ptr, shape, dtype_code, gpu_id, owner):
+    def __init__(self, ptr, shape, dtype_code, gpu_id, owner, row_indexed=True):
+        self._row_indexed = row_indexed   # leading dimension = live agents (buffer holds `capacity` rows)
         self._ptr = ptr
         self._shape = tuple(int(x) for x in shape)
         self._code = dtype_code
@@ -57,7 +58,21 @@ class Tensor:
         dev = torch.device("cuda", self._gpu_id)
         if self._shape[0] == 0:
             return torch.empty(self._shape, dtype=dt, device=dev)
-        t = torch.as_tensor(self, device=dev)
+        # The library keeps every export at a fixed address, allocated for `capacity` rows: wrap the
+        # pointer once per (address, dtype, columns) and re-slice that view to the live row count --
+        # re-wrapping through __cuda_array_interface__ costs tens of microseconds per call.
+        cache = getattr(self._owner, "_views", None)
+        cap = getattr(self._owner, "_row_capacity", 0)
+        if cache is None or not self._row_indexed or self._shape[0] > cap:
+            t = torch.as_tensor(self, device=dev)
+        else:
+            key = (self._ptr, self._code, self._shape[1])
+            base = cache.get(key)
+            if base is None:
+                base = torch.as_tensor(Tensor(self._ptr, (cap, self._shape[1]), self._code, self._gpu_id,
+                                              None), device=dev)
+                cache[key] = base
+            t = base[: self._shape[0]]
         assert t.data_ptr() == self._ptr, "expected a zero-copy view"
         return t
 
@@ -75,6 +90,10 @@ class SimManager:
         cfg = _native.Config(int(gpu_id), int(num_worlds), int(rand_seed) & 0xFFFFFFFF,
                              int(init_num_agents_per_world), int(max_agents_per_world), int(world_id_offset))
         _native.check(self._lib.mbots_create_ex(ctypes.byref(cfg), ctypes.byref(self._h)), "mbots_create_ex")
+        cap = ctypes.c_uint64()
+        _native.check(self._lib.mbots_row_capacity(self._h, ctypes.byref(cap)), "mbots_row_capacity")
+        self._row_capacity = int(cap.value)
+        self._views = {}
 
     def __del__(self):
         h = getattr(self, "_h", None)
@@ -110,7 +129,9 @@ class SimManager:
         dt = ctypes.c_int32()
         _native.check(self._lib.mbots_tensor(self._h, EXPORT[name], ctypes.byref(ptr), dims, ctypes.byref(dt)),
                       f"mbots_tensor({name})")
-        return Tensor(ptr.value or 0, (dims[0], dims[1]), dt.value, self._gpu_id, self)
+        per_world = name in ("RESET", "SPECIES_COUNT", "DEBUG_FOOD", "DEBUG_ROW_BASE") or name.startswith("DEBUG_WORLD") \
+            or name in ("DEBUG_RNG_COUNT", "DEBUG_NUM_FOOD")
+        return Tensor(ptr.value or 0, (dims[0], dims[1]), dt.value, self._gpu_id, self, row_indexed=not per_world)
 
     def _pair(self, cur, prev, is_prev):
         return self.export(prev if is_prev else cur)
