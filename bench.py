@@ -204,6 +204,26 @@ def cpu_baseline_sample(target_seconds=12.0):
                       f"{cores} threads"}
 
 
+def bind_host_to_gpu(local_rank):
+    """Multi-GPU runs: pin this rank's host threads (and so its first-touch pinned staging buffers) to the
+    CPUs NVML reports as local to its GPU, so that the e2e leg's PCIe copies do not cross the socket
+    interconnect. Returns the number of CPUs bound to, or None when nothing was changed."""
+    try:
+        import pynvml
+        pynvml.nvmlInit()
+        h = pynvml.nvmlDeviceGetHandleByIndex(local_rank)
+        ncpu = os.cpu_count() or 1
+        mask = pynvml.nvmlDeviceGetCpuAffinity(h, (ncpu + 63) // 64)
+        local = {i for i in range(ncpu) if (int(mask[i // 64]) >> (i % 64)) & 1}
+        cpus = sorted(local & os.sched_getaffinity(0))
+        if not cpus or len(cpus) == len(os.sched_getaffinity(0)):
+            return None
+        os.sched_setaffinity(0, cpus)
+        return len(cpus)
+    except Exception:
+        return None
+
+
 # ------------------------------------------------------------------------------------------------
 def run_ours(args, rank, world, local_rank):
     import numpy as np
@@ -213,10 +233,11 @@ def run_ours(args, rank, world, local_rank):
     from madrona_bots.sharding import allreduce_max, allreduce_stats
 
     assert torch.cuda.is_available(), "bench.py needs a CUDA device (no CPU fallback)"
+    bound_cpus = bind_host_to_gpu(local_rank) if world > 1 else None
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
     W = args.worlds_per_gpu
-    sim = SimManager(local_rank, W, SEED, INIT_AGENTS, world_id_offset=rank * W)
+    sim = SimManager(local_rank, W, SEED, INIT_AGENTS, world_id_offset=rank * W, max_agents_per_world=args.cap)
     rows_cap = W * 48                               # the population stays near 33 agents/world (max ~41)
 
     host_pool = [torch.from_numpy(a).pin_memory() for a in one_hot_pool_numpy(rows_cap, 1234 + rank)]
@@ -319,7 +340,9 @@ def run_ours(args, rank, world, local_rank):
     line = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": ms_max / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-        "dtype": "f32+i32", "data": "synthetic", "config": workload_config(args),
+        "dtype": "f32+i32", "data": "synthetic",
+        "config": dict(workload_config(args), host_affinity=(f"rank bound to its GPU's {bound_cpus} local CPUs (NVML)"
+                                                              if bound_cpus else "unchanged")),
         "clocks": clocks, "gpu_launches": int(launches),
         "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d // max(1, args.steps),
                 "d2h_bytes_per_step": d2h // max(1, args.steps), "ms_per_step": ms_e / args.steps},
@@ -348,6 +371,7 @@ def main():
     ap.add_argument("--worlds-per-gpu", type=int, default=65536)
     ap.add_argument("--ref-worlds", type=int, default=4096, help="worlds per step of the CPU reference arm")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--cap", type=int, default=0, help="per-world slot capacity (0 = library default, 128)")
     args = ap.parse_args()
     if args.warmup < 3:
         args.warmup = 3
@@ -359,6 +383,8 @@ def main():
     if args.impl == "reference":
         run_reference(args, rank, world)
         return
+    # stdout carries exactly one JSON line: NCCL's own banner / debug output goes to stderr
+    os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
     if world > 1:
         import torch
         import torch.distributed as dist

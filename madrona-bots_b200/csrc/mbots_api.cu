@@ -163,7 +163,7 @@ int enqueue_repack(mbots_sim *s, cudaStream_t st, int with_sensors, int count_st
     CU(cudaGetLastError());
     CU(cudaMemcpyAsync(s->hTotals, s->d.totals, sizeof(Totals), cudaMemcpyDeviceToHost, st));
     s->cur ^= 1;
-    s->launches += 1 + (uint64_t)nexp;
+    s->launches += 2 + (uint64_t)nexp;                  /* tile sums, row scan, export variant(s) */
     s->dirty = true;
     return MBOTS_OK;
 }

@@ -63,7 +63,7 @@ struct SimDev {
     int32_t *numFood;         /* Sim::currentNumFood */
     uint2 *food;              /* [numWorlds * 48]: byte p<5 = (x<<4|y) of package p, byte 5 = has-food mask */
     int4 *speciesLive;        /* rows per (world, species) after respawn: input of the row scan */
-    TileSum *tileSum[2];      /* per-tile sums of speciesLive, accumulated by the step that owns parity `cur` */
+    TileSum *tileSum[2];      /* per-tile sums of speciesLive (tile_sum_kernel), indexed by the parity of the step */
     int4 *rowBase[2];         /* first row of (world, species) in obs set 0 / 1 */
     int4 *speciesCount;       /* export SpeciesCount (tracker counts, before respawn) */
     float4 *speciesReward;    /* SpeciesReward */

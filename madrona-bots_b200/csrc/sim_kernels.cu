@@ -67,9 +67,6 @@ __global__ void init_kernel(SimDev d)
         const int q = (int)(d.initAgents / kNumSpecies), r = (int)(d.initAgents % kNumSpecies);
         c.x = q + (r > 0); c.y = q + (r > 1); c.z = q + (r > 2); c.w = q;
         d.speciesLive[w] = c;
-        TileSum *ts = d.tileSum[0] + (w / kScanTile);
-        atomicAdd(&ts->c[0], c.x); atomicAdd(&ts->c[1], c.y); atomicAdd(&ts->c[2], c.z); atomicAdd(&ts->c[3], c.w);
-        atomicMax(&ts->maxCount, (int)d.initAgents);
         d.speciesCount[w] = make_int4(0, 0, 0, 0);
         d.speciesReward[w] = make_float4(0.f, 0.f, 0.f, 0.f);
         d.speciesHealth[w] = make_int4(0, 0, 0, 0);
@@ -127,7 +124,7 @@ __device__ __forceinline__ uint32_t food_match(const uint2 &f, uint32_t cell)
 
 __device__ __forceinline__ int warp_sum(int v) { return __reduce_add_sync(FULL, v); }
 
-__global__ void __launch_bounds__(kStepWarps * 32) step_kernel(SimDev d, int cur, uint32_t slots)
+__global__ void __launch_bounds__(kStepWarps * 32, 8) step_kernel(SimDev d, int cur, uint32_t slots)
 {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -150,39 +147,60 @@ __global__ void __launch_bounds__(kStepWarps * 32) step_kernel(SimDev d, int cur
     const unsigned lt = (1u << lane) - 1u;
 
     /* ---- P0: stage the world: state, the action row of every agent, food; reset the chunk counters ---- */
-    /* the first 32 slots are loaded before the live count is known (slots < cap always exist): one DRAM round
-     * trip less on the critical path of nearly every world */
-    float4 pose0 = d.pose[base + lane];
-    int hp0 = d.health[base + lane];
-    uint32_t sp0 = d.species[base + lane];
-    int tgt0 = d.target[base + lane];
-    int row0 = d.row[base + lane];
+    /* Two DRAM round trips for a world of up to 64 agents: (1) the state of slots lane and lane + 32 (requested
+     * before the live count is known -- slots below the capacity always exist), the per-world scalars and the
+     * food records; (2) the action rows, whose addresses come from (1). Larger worlds take further passes. */
+    const bool has_b = 32u + (uint32_t)lane < cap;
+    const size_t ia = base + lane, ib = base + 32 + (has_b ? lane : 0);
+    float4 pose_a = d.pose[ia], pose_b = d.pose[ib];
+    int hp_a = d.health[ia], hp_b = d.health[ib];
+    uint32_t sp_a = d.species[ia], sp_b = d.species[ib];
+    int tgt_a = d.target[ia], tgt_b = d.target[ib];
+    int row_a = d.row[ia], row_b = d.row[ib];
     const int n0 = d.worldCount[w];
     const uint2 kk = d.rngKey[w];
     const uint32_t rng0 = d.rngCount[w];
     int numFood = d.numFood[w];
-    for (int s = lane; s < n0; s += 32) {
-        if (s >= 32) {
-            pose0 = d.pose[base + s];
-            hp0 = d.health[base + s];
-            sp0 = d.species[base + s];
-            tgt0 = d.target[base + s];
-            row0 = d.row[base + s];
-        }
-        const int2 *ap = reinterpret_cast<const int2 *>(from.action + (size_t)row0 * 6);
-        const int2 a0 = ap[0], a1 = ap[1], a2 = ap[2];
+    static_assert(kNumChunks == 48, "two loads per lane cover the chunk records");
+    const uint2 food0 = d.food[(size_t)w * kNumChunks + lane];
+    const uint2 food1 = d.food[(size_t)w * kNumChunks + 32 + (lane & 15)];
+    auto park = [&](int s, const float4 &pose, int hp, uint32_t sp, int tgt, int row, const int2 &a0, const int2 &a1,
+                    const int2 &a2) {
         const uint32_t act = (a0.x != 0) | ((a0.y != 0) << 1) | ((a1.x != 0) << 2) | ((a1.y != 0) << 3) |
                              ((a2.x != 0) << 4) | ((a2.y != 0) << 5);
-        spose[s] = pose0;
-        accum[s] = hp0;
-        soldrow[s] = row0;
-        spec[s] = (uint8_t)sp0;
-        sinfo[s] = act | (sp0 << 10) | ((uint32_t)(tgt0 + 1) << 13);
+        spose[s] = pose;
+        accum[s] = hp;
+        soldrow[s] = row;
+        spec[s] = (uint8_t)sp;
+        sinfo[s] = act | (sp << 10) | ((uint32_t)(tgt + 1) << 13);
+    };
+    {
+        const bool on_a = lane < n0, on_b = has_b && 32 + lane < n0;
+        const int2 zero = make_int2(0, 0);
+        int2 a0 = zero, a1 = zero, a2 = zero, b0 = zero, b1 = zero, b2 = zero;
+        if (on_a) {
+            const int2 *ap = reinterpret_cast<const int2 *>(from.action + (size_t)row_a * 6);
+            a0 = ap[0]; a1 = ap[1]; a2 = ap[2];
+        }
+        if (on_b) {
+            const int2 *bp = reinterpret_cast<const int2 *>(from.action + (size_t)row_b * 6);
+            b0 = bp[0]; b1 = bp[1]; b2 = bp[2];
+        }
+        if (on_a) park(lane, pose_a, hp_a, sp_a, tgt_a, row_a, a0, a1, a2);
+        if (on_b) park(32 + lane, pose_b, hp_b, sp_b, tgt_b, row_b, b0, b1, b2);
     }
-    for (int c = lane; c < kNumChunks; c += 32) {
-        chunkAgents[c] = 0;                             /* resetChunkInfoSystem (:390-396) */
-        chunkSpeed[c] = 0;
-        food[c] = d.food[(size_t)w * kNumChunks + c];
+    for (int s = 64 + lane; s < n0; s += 32) {
+        const int row = d.row[base + s];
+        const int2 *ap = reinterpret_cast<const int2 *>(from.action + (size_t)row * 6);
+        park(s, d.pose[base + s], d.health[base + s], d.species[base + s], d.target[base + s], row, ap[0], ap[1], ap[2]);
+    }
+    chunkAgents[lane] = 0;                              /* resetChunkInfoSystem (:390-396) */
+    chunkSpeed[lane] = 0;
+    food[lane] = food0;
+    if (lane < kNumChunks - 32) {
+        chunkAgents[32 + lane] = 0;
+        chunkSpeed[32 + lane] = 0;
+        food[32 + lane] = food1;
     }
     __syncwarp();
 
@@ -379,11 +397,6 @@ __global__ void __launch_bounds__(kStepWarps * 32) step_kernel(SimDev d, int cur
         d.worldCount[w] = count1;
         d.rngCount[w] = rngBase + 2u * needTotal;
         d.numFood[w] = numFood;
-        /* partial sums of the row scan: one tile = kScanTile consecutive worlds */
-        TileSum *ts = d.tileSum[cur] + (w / kScanTile);
-#pragma unroll
-        for (int k = 0; k < 4; ++k) if (lr[k]) atomicAdd(&ts->c[k], lr[k]);
-        atomicMax(&ts->maxCount, count1);
         const uint32_t deaths = (uint32_t)(n0 - nLive);
         const uint32_t overflow = (uint32_t)(nBreed - bornOk) + (needTotal - respOk);
         /* cumulative event counters: fire-and-forget reductions, nothing waits on them */
@@ -417,9 +430,33 @@ __device__ __forceinline__ int warp_incl_scan(int v)
     return v;
 }
 
-/* One CTA per tile of 1,024 worlds, no inter-CTA dependency: the per-tile partial sums were
- * accumulated by step_kernel (tileSum[cur]); every CTA reduces them to the species totals and to
- * the prefix of its own tile, then scans its worlds. Also zeroes tileSum[cur ^ 1] for the next step. */
+/* tile_sum_kernel: per-tile partial sums of the row scan, one CTA per tile of 1,024 worlds. (Accumulating
+ * them with atomics from step_kernel put every concurrently running world on the same five addresses; the L2
+ * serialises same-address atomics, and that backlog -- not DRAM -- set step_kernel's duration.) */
+__global__ void __launch_bounds__(kScanTile) tile_sum_kernel(SimDev d, int cur)
+{
+    __shared__ int red[32][5];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int w = blockIdx.x * kScanTile + tid;
+    int4 c = make_int4(0, 0, 0, 0);
+    if (w < (int)d.numWorlds) c = d.speciesLive[w];
+    int v[5] = {c.x, c.y, c.z, c.w, c.x + c.y + c.z + c.w};
+#pragma unroll
+    for (int k = 0; k < 5; ++k) {
+        const int r = k == 4 ? __reduce_max_sync(FULL, v[k]) : __reduce_add_sync(FULL, v[k]);
+        if (lane == 0) red[warp][k] = r;
+    }
+    __syncthreads();
+    if (tid < 5) {
+        int a = 0;
+        for (int i = 0; i < kScanTile / 32; ++i) a = tid == 4 ? max(a, red[i][tid]) : a + red[i][tid];
+        TileSum *ts = d.tileSum[cur] + blockIdx.x;
+        if (tid == 4) ts->maxCount = a; else ts->c[tid] = a;
+    }
+}
+
+/* One CTA per tile of 1,024 worlds, no inter-CTA dependency: every CTA reduces the per-tile partial sums
+ * (tile_sum_kernel) to the species totals and to the prefix of its own tile, then scans its worlds. */
 __global__ void __launch_bounds__(kScanTile) scan_kernel(SimDev d, int cur, int count_step)
 {
     __shared__ int red[32][9];
@@ -483,8 +520,6 @@ __global__ void __launch_bounds__(kScanTile) scan_kernel(SimDev d, int cur, int 
         d.worldOffset[w] = base[4];
     }
     if (tile == 0) {
-        TileSum z = {{0, 0, 0, 0}, 0, {0, 0, 0}};
-        for (int t = tid; t < nt; t += kScanTile) d.tileSum[cur ^ 1][t] = z;
         if (tid == 0) {
             for (int k = 0; k < 4; ++k) d.totals->speciesTotal[k] = (uint32_t)fin[k];
             d.totals->totalAgents = (uint32_t)spBase;
@@ -977,7 +1012,9 @@ void launch_step(const SimDev &d, int cur, uint32_t slots, cudaStream_t s)
 
 void launch_scan(const SimDev &d, int cur, int count_step, cudaStream_t s)
 {
-    scan_kernel<<<(d.numWorlds + kScanTile - 1) / kScanTile, kScanTile, 0, s>>>(d, cur, count_step);
+    const unsigned tiles = (d.numWorlds + kScanTile - 1) / kScanTile;
+    tile_sum_kernel<<<tiles, kScanTile, 0, s>>>(d, cur);
+    scan_kernel<<<tiles, kScanTile, 0, s>>>(d, cur, count_step);
 }
 
 template <bool FAST>
