@@ -45,6 +45,9 @@ POOL = 4                       # pre-generated action buffers, cycled
 ALGO_BYTES = {"step": 24 + 28 + 24 + 9.0, "export_sense": 44 + 64 + 64 + 64, "shift": 264}
 # bytes the export kernel really has to move per agent given that rows move every step:
 MOVED_BYTES_EXPORT = 280 + 280 + 36 + 64 + 4 + 2 + 41
+# dram__bytes_read.sum + dram__bytes_write.sum of export_kernel<FAST> per agent, from the committed
+# `ncu --set full` capture (profiles/r1d_ncu_full_summary.txt: 705.4 MB + 809.1 MB at 2,173,116 agents)
+NCU_TRAFFIC_BYTES_PER_AGENT_EXPORT = (705.409024e6 + 809.079040e6) / 2173116.0
 
 
 def measured_peaks():
@@ -348,7 +351,9 @@ def run_ours(args, rank, world, local_rank):
                 "d2h_bytes_per_step": d2h // max(1, args.steps), "ms_per_step": ms_e / args.steps},
         "roofline": {"bound": "hbm", "kernel": "export_kernel (row carry + observation export + 32-ray sensor)",
                      "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                     "traffic": None, "peak_source": peak_src,
+                     "traffic": NCU_TRAFFIC_BYTES_PER_AGENT_EXPORT * agents_per_launch,
+                     "traffic_source": "ncu --set full capture under profiles/ (bytes per agent x agents of this run)",
+                     "peak_source": peak_src,
                      "algo_bytes_per_agent": ALGO_BYTES["export_sense"],
                      "moved_bytes_per_agent": MOVED_BYTES_EXPORT,
                      "achieved_moved": MOVED_BYTES_EXPORT * agents_per_launch / (k_ms * 1e-3) / 1e9 if k_ms > 0 else 0.0,

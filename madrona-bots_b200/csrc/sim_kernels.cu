@@ -124,7 +124,10 @@ __device__ __forceinline__ uint32_t food_match(const uint2 &f, uint32_t cell)
 
 __device__ __forceinline__ int warp_sum(int v) { return __reduce_add_sync(FULL, v); }
 
-__global__ void __launch_bounds__(kStepWarps * 32, 8) step_kernel(SimDev d, int cur, uint32_t slots)
+#ifndef MBK_STEP_MIN_BLOCKS
+#define MBK_STEP_MIN_BLOCKS 8
+#endif
+__global__ void __launch_bounds__(kStepWarps * 32, MBK_STEP_MIN_BLOCKS) step_kernel(SimDev d, int cur, uint32_t slots)
 {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -378,16 +381,23 @@ __global__ void __launch_bounds__(kStepWarps * 32, 8) step_kernel(SimDev d, int 
             d.scratch[o] = make_float4(__int_as_float(-1), 0.f, 0.f, __int_as_float(0));
         }
     }
+    /* the species reward terms cost three IEEE divisions each: lane k computes species k, lane 0 collects */
+    float rmine;
+    {
+        const int k = lane & 3;
+        const int ck = k == 0 ? cnt[0] : k == 1 ? cnt[1] : k == 2 ? cnt[2] : cnt[3];
+        const int hk = k == 0 ? hsum[0] : k == 1 ? hsum[1] : k == 2 ? hsum[2] : hsum[3];
+        rmine = species_reward((uint32_t)ck, (uint32_t)hk, d.initAgents);
+    }
+    const float4 rw = make_float4(__shfl_sync(FULL, rmine, 0), __shfl_sync(FULL, rmine, 1), __shfl_sync(FULL, rmine, 2),
+                                  __shfl_sync(FULL, rmine, 3));
     if (lane == 0) {
         int4 liveRows;
         int *lr = &liveRows.x;
-        float4 rw;
-        float *rwp = &rw.x;
 #pragma unroll
         for (int k = 0; k < 4; ++k) {
             const uint32_t ok = respOk > pre[k] ? (respOk - pre[k] < need[k] ? respOk - pre[k] : need[k]) : 0u;
             lr[k] = cnt[k] + (int)ok;
-            rwp[k] = species_reward((uint32_t)cnt[k], (uint32_t)hsum[k], d.initAgents);
         }
         const int count1 = nLive + bornOk + (int)respOk;
         d.speciesLive[w] = liveRows;

@@ -4,7 +4,8 @@ import ctypes
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(os.path.dirname(_HERE), "lib", "libmbots.so")
+# MBOTS_LIB selects another build of the same library (A/B runs of kernel variants); default = in-tree build
+LIB_PATH = os.environ.get("MBOTS_LIB") or os.path.join(os.path.dirname(_HERE), "lib", "libmbots.so")
 
 # mbots_export_id
 EXPORT = dict(
