@@ -594,7 +594,7 @@ __host__ __device__ inline ExportLayout export_layout(uint32_t slots, uint32_t t
     L.newrow = o; o += slots * 4;
     L.oldrow = o; o += slots * 4;
     L.theta = o; o += slots * 4;
-    L.spec = o; o += (slots + 15u) & ~15u;
+    L.spec = o; o += slots < 64u ? 64u : (slots + 15u) & ~15u;   /* FAST reads the 0xff sentinel at [63] */
     L.total = (o + 15u) & ~15u;
     return L;
 }
@@ -664,6 +664,7 @@ __device__ __forceinline__ void export_world(const SimDev &d, int cur, int with_
     const float4 srew = d.speciesReward[w];
     const unsigned lt = (1u << lane) - 1u;
 
+    if (FAST && lane == 0) spec[63] = 0xffu;            /* species byte a missed ray decodes to (n <= 63) */
     /* ---- per agent (one lane each): new row, observation exports, small carried columns ---- */
     int seen[4] = {0, 0, 0, 0};                         /* agents of each species in lower passes */
     for (int s0 = 0; s0 < n; s0 += 32) {
@@ -868,25 +869,40 @@ __device__ __forceinline__ void export_world(const SimDev &d, int cur, int with_
         for (int idx = lane; idx < m * 8; idx += 32) {
             const int ol = idx >> 3, quad = idx & 7, i = tile0 + ol;
             const int row = newrow[i];
-            Key key[4];
+            uint32_t dep = 0, sem = 0;
             if (FAST) {
+                /* A 32-bit key decodes without a hit / miss branch: the miss key 0xffffffff carries slot 63, whose
+                 * species byte is the 0xff sentinel (FAST worlds hold at most 63 agents), and its time field is
+                 * 255.99998f, i.e. depth 255 -- exactly what a miss exports. */
                 const uint4 v = reinterpret_cast<const uint4 *>(best)[idx];
-                key[0] = (Key)v.x; key[1] = (Key)v.y; key[2] = (Key)v.z; key[3] = (Key)v.w;
+                const uint32_t key[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+                for (int k = 0; k < 4; ++k) {
+                    const uint32_t dv = (uint32_t)(uint8_t)(int)S::t((Key)key[k]);
+                    const uint32_t sv = (uint32_t)spec[key[k] & 63u];
+                    dep |= dv << (8 * k);
+                    sem |= sv << (8 * k);
+                }
+                if (quad == 0) dep = (dep & ~0xffu) | ((uint32_t)row & 0xffu);          /* "sanity" overwrite (U9) */
+                if (quad == kFinderRay / 4) {
+                    const uint32_t fk = key[kFinderRay % 4];
+                    d.target[base + i] = (int16_t)(fk != 0xffffffffu ? (int)(fk & 63u) : -1);
+                }
             } else {
+                Key key[4];
 #pragma unroll
                 for (int k = 0; k < 4; ++k) key[k] = best[idx * 4 + k];
-            }
-            uint32_t dep = 0, sem = 0;
 #pragma unroll
-            for (int k = 0; k < 4; ++k) {
-                const bool hit = key[k] != S::kMiss;
-                const int slot = hit ? S::slot(key[k]) : -1;
-                uint32_t dv = hit ? (uint32_t)(uint8_t)(int)S::t(key[k]) : 255u;
-                const uint32_t sv = hit ? (uint32_t)spec[slot] : 0xffu;
-                if (quad == 0 && k == 0) dv = (uint32_t)row & 0xffu;      /* "sanity" overwrite (U9) */
-                if (quad == kFinderRay / 4 && k == kFinderRay % 4) d.target[base + i] = (int16_t)slot;
-                dep |= dv << (8 * k);
-                sem |= sv << (8 * k);
+                for (int k = 0; k < 4; ++k) {
+                    const bool hit = key[k] != S::kMiss;
+                    const int slot = hit ? S::slot(key[k]) : -1;
+                    uint32_t dv = hit ? (uint32_t)(uint8_t)(int)S::t(key[k]) : 255u;
+                    const uint32_t sv = hit ? (uint32_t)spec[slot] : 0xffu;
+                    if (quad == 0 && k == 0) dv = (uint32_t)row & 0xffu;      /* "sanity" overwrite (U9) */
+                    if (quad == kFinderRay / 4 && k == kFinderRay % 4) d.target[base + i] = (int16_t)slot;
+                    dep |= dv << (8 * k);
+                    sem |= sv << (8 * k);
+                }
             }
             reinterpret_cast<uint32_t *>(to.depth)[(size_t)row * 8 + quad] = dep;
             reinterpret_cast<uint32_t *>(to.semantic)[(size_t)row * 8 + quad] = sem;
@@ -910,7 +926,7 @@ export_kernel(SimDev d, int cur, int with_sensors, uint32_t slots, uint32_t tile
         const uint32_t w = blockIdx.x * kExportWarps + warp;
         if (w >= d.numWorlds) return;               /* whole warp: no block-level barrier anywhere */
         const int n = d.worldCount[w];
-        if (n > (int)slots) return;
+        if (n > (int)slots || n > 63) return;       /* slot 63 is the miss sentinel of the 32-bit keys */
         export_world<FAST>(d, cur, with_sensors, slots, tile, w, n, my);
     } else {
         for (uint32_t w = blockIdx.x * kExportWarps + warp; w < d.numWorlds; w += gridDim.x * kExportWarps) {
@@ -1053,7 +1069,7 @@ int launch_export(const SimDev &d, int cur, int with_sensors, uint32_t bound, cu
     if (tile < 40u) tile = 40u;
     if (tile > fast_slots) tile = fast_slots;
     launch_export_variant<true>(d, cur, with_sensors, fast_slots, tile, 0, s);
-    launch_export_variant<false>(d, cur, with_sensors, d.cap, kFullTile, (int)fast_slots, s);
+    launch_export_variant<false>(d, cur, with_sensors, d.cap, kFullTile, (int)(fast_slots < 63u ? fast_slots : 63u), s);
     return 2;
 }
 

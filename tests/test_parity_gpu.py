@@ -43,6 +43,16 @@ def test_ragged_init(cuda_device, init_agents):
     drive(o, g, steps=60, seed=2, mode="bits")
 
 
+@pytest.mark.parametrize("init_agents,cap", [(60, 64), (56, 96), (44, 64)])
+def test_worlds_around_the_fast_sensor_limit(cuda_device, init_agents, cap):
+    """The sensor's fast variant (32-bit nearest-hit keys, slot 63 = miss sentinel) takes worlds of up to 63
+    agents, the full variant the rest: populations that cross 63 / 64 in both directions."""
+    o, g = make_pair(24, 21, init_agents, cap=cap)
+    counts = drive(o, g, steps=50, seed=13, mode="bits", check_every=5)
+    wc = o.tensor("DEBUG_WORLD_COUNT")[:, 0]
+    assert max(counts) > 24 * 40 and wc.max() <= cap
+
+
 def test_zero_agents(cuda_device):
     o, g = make_pair(8, 1, 0)
     drive(o, g, steps=5, seed=2)
