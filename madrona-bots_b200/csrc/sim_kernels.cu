@@ -742,7 +742,7 @@ __device__ __forceinline__ void export_world(const SimDev &d, int cur, int with_
      *  1. cull. Within a tile, blocks of <= 32 observers are spread over the lanes as an (observer x target)
      *     grid -- 32 x 1, or for the last few observers 8 x 4 ... 1 x 32 -- so a lane keeps its observer in
      *     registers and steps through the targets with no index arithmetic. Per pair: conservative candidate
-     *     rays (pair_candidates, ~0.27 per pair). Pairs with candidates are ballot-compacted into a pair queue.
+     *     rays of one fan (pair_run, ~0.27 per pair). Pairs with candidates are ballot-compacted into a pair queue.
      *  2. expand. 32 queued pairs at a time: a warp scan of their candidate counts, then every lane of a
      *     32-test chunk finds the pair that owns its slot by binary search over the scan (shuffles only, no
      *     divergence) and queues (observer, target, ray).
@@ -778,12 +778,8 @@ __device__ __forceinline__ void export_world(const SimDev &d, int cur, int with_
          * lane occupancy and with no queue traffic (most pairs have exactly one); the others are expanded into
          * the test queue. `flush`: also run a last partial chunk of queued tests. */
         auto expand = [&](uint32_t info, bool valid, bool flush) {
-            if (valid) {
-                const int cf = (int)((info >> 5) & 31u);
-                test((int)(info >> (17 + JB)), (int)((info >> 17) & ((1u << JB) - 1u)),
-                     cf > 0 ? (int)(info & 31u) : kFwdRays + (int)((info >> 10) & 7u));
-            }
-            const int c = valid ? (int)((info >> 5) & 31u) + (int)((info >> 13) & 15u) - 1 : 0;
+            if (valid) test((int)(info >> (17 + JB)), (int)((info >> 17) & ((1u << JB) - 1u)), (int)(info & 31u));
+            const int c = valid ? (int)((info >> 5) & 63u) - 1 : 0;
             int inc = c;
 #pragma unroll
             for (int o = 1; o < 32; o <<= 1) {
@@ -801,9 +797,7 @@ __device__ __forceinline__ void export_world(const SimDev &d, int cur, int with_
                     if (v <= q) own += st;
                 }
                 const uint32_t oi = __shfl_sync(FULL, info, own);
-                const int k = q - __shfl_sync(FULL, exc, own) + 1;   /* candidate 0 was tested above */
-                const int ocf = (int)((oi >> 5) & 31u);
-                const int r = k < ocf ? (int)(oi & 31u) + k : kFwdRays - ocf + (int)((oi >> 10) & 7u) + k;
+                const int r = (int)(oi & 31u) + q - __shfl_sync(FULL, exc, own) + 1;   /* candidate 0 was tested above */
                 if (q < total) queue[qn + lane] = ((oi >> 17) << 5) | (uint32_t)r;
                 qn += max(0, min(32, total - q0));
                 __syncwarp();
@@ -822,11 +816,10 @@ __device__ __forceinline__ void export_world(const SimDev &d, int cur, int with_
         auto spans = [&](uint32_t code, bool valid) {
             const int ol = (int)(code >> JB), j = (int)(code & ((1u << JB) - 1u));
             const float2 pi = pos[tile0 + ol], hd = head[tile0 + ol], pj = pos[j];
-            const RayCount rc = pair_spans(pi.x - pj.x, pi.y - pj.y, Dir{hd.x, hd.y});
-            /* flo 0-4 | cf 5-9 | blo 10-12 | cb 13-16 | target 17.. (JB bits) | observer of the tile */
-            const uint32_t info = (uint32_t)(rc.flo & 31) | ((uint32_t)rc.cf << 5) | ((uint32_t)(rc.blo & 7) << 10) |
-                                  ((uint32_t)rc.cb << 13) | (code << 17);
-            const bool has = valid && (rc.cf + rc.cb) > 0;
+            const RayRun rr = pair_run(pi.x - pj.x, pi.y - pj.y, Dir{hd.x, hd.y});
+            /* first ray 0-4 | rays 5-10 | target 17.. (JB bits) | observer of the tile */
+            const uint32_t info = (uint32_t)(rr.lo & 31) | ((uint32_t)rr.count << 5) | (code << 17);
+            const bool has = valid && rr.count > 0;
             const unsigned bal = __ballot_sync(FULL, has);
             if (has) pairq[pqn + __popc(bal & lt)] = info;
             pqn += __popc(bal);

@@ -342,11 +342,16 @@ MBP_HD int cull_floor(float v)
 
 /* oc = observer - target, h = unit heading of the observer. Cull arithmetic only: explicit FMAs are fine
  * here (nothing below feeds a result, only the choice of which exact tests to run). Straight-line code (the
- * kernel runs it on every lane of a warp): returns the forward span [flo, flo + cf) and the backward span
- * [blo, blo + cb) as counts; both counts are 0 for a pair that cannot produce an accepted hit. */
-struct RayCount { int flo, cf, blo, cb; };
+ * kernel runs it on every lane of a warp): returns the run of candidate rays [lo, lo + count) in sensor
+ * numbering (forward fan 0..23, backward fan 24..31); count == 0 for a pair that cannot produce an accepted hit.
+ * A target is in front of the observer or behind it, so only one fan is evaluated: a target behind is mirrored
+ * through the observer (direction (-along, -left)) and looked up in the backward fan's ray spacing. Only a
+ * target closer than 1.5 (angular half-width above pi/4) can reach both fans: all 32 rays are candidates then. */
+struct RayRun { int lo, count; };
 
-MBP_HD RayCount pair_spans(float ocx, float ocy, Dir h)
+constexpr float kCullBothFansDist2 = 2.25f;
+
+MBP_HD RayRun pair_run(float ocx, float ocy, Dir h)
 {
     const float d2 = mb_fmaf(ocx, ocx, ocy * ocy);
     const bool far_enough = d2 >= kCullMinDist2;                 /* false also for NaN */
@@ -355,32 +360,31 @@ MBP_HD RayCount pair_spans(float ocx, float ocy, Dir h)
     /* direction to the target (-oc) in the heading frame: along, left */
     const float al = -mb_fmaf(ocx, h.x, ocy * h.y);
     const float lf = mb_fmaf(ocx, h.y, -(ocy * h.x));
-    const float rho = cull_atan2(lf, al);                         /* in [-pi, pi] */
+    const bool back = al < 0.f;
+    const float rho = cull_atan2(back ? -lf : lf, fabsf(al));      /* in [-pi/2, pi/2], about the fan's own axis */
     constexpr float inv_df = ((float)kFwdRays - 1.f) / (kPi * 0.5f);
     constexpr float inv_db = ((float)(kSensor - kFwdRays) - 1.f) / (kPi * 0.5f);
+    const float inv_d = back ? inv_db : inv_df;
+    const int last = back ? kSensor - kFwdRays - 1 : kFwdRays - 1;
     /* ray k of a fan sits at (k / inv_d - pi/4) from the fan axis: candidates are ceil(rs - hs) .. floor(rs + hs) */
-    const float rsf = mb_fmaf(rho, inv_df, kPi * 0.25f * inv_df), hsf = half * inv_df;
-    int flo = cull_ceil(rsf - hsf), fhi = cull_floor(rsf + hsf);
-    flo = flo < 0 ? 0 : flo;
-    fhi = fhi > kFwdRays - 1 ? kFwdRays - 1 : fhi;
-    const float rb = rho < 0.f ? rho + kPi : rho - kPi;
-    const float rsb = mb_fmaf(rb, inv_db, kPi * 0.25f * inv_db), hsb = half * inv_db;
-    int blo = cull_ceil(rsb - hsb), bhi = cull_floor(rsb + hsb);
-    blo = blo < 0 ? 0 : blo;
-    bhi = bhi > kSensor - kFwdRays - 1 ? kSensor - kFwdRays - 1 : bhi;
-    RayCount rc;
-    rc.flo = flo; rc.blo = blo;
-    rc.cf = far_enough && fhi >= flo ? fhi - flo + 1 : 0;
-    rc.cb = far_enough && bhi >= blo ? bhi - blo + 1 : 0;
-    return rc;
+    const float rs = mb_fmaf(rho, inv_d, kPi * 0.25f * inv_d), hs = half * inv_d;
+    int lo = cull_ceil(rs - hs), hi = cull_floor(rs + hs);
+    lo = lo < 0 ? 0 : lo;
+    hi = hi > last ? last : hi;
+    RayRun rr;
+    rr.lo = back ? kFwdRays + lo : lo;
+    rr.count = hi >= lo ? hi - lo + 1 : 0;
+    if (d2 < kCullBothFansDist2) { rr.lo = 0; rr.count = kSensor; }
+    if (!far_enough) rr.count = 0;
+    return rr;
 }
 
 /* First, cheap stage of the cull: can the pair have candidates at all? Both fans together cover the double
  * wedge |left| <= |along| around the heading axis. With psi the angle between the target direction and that
- * axis, pair_spans() yields candidates only when psi <= pi/4 + half, and
+ * axis, pair_run() yields candidates only when psi <= pi/4 + half, and
  *   |left| - |along| = D * sqrt(2) * sin(psi - pi/4)  <=  D * sqrt(2) * sin(half)  <  1.54
  * for every D in [1.095, 200] (half >= pi/4 only below D = 1.47, where |left| - |along| <= D anyway). Half of
- * all pairs fail this and never reach pair_spans(). */
+ * all pairs fail this and never reach pair_run(). */
 constexpr float kCullWedgeSlack = 1.6f;
 
 MBP_HD bool pair_maybe(float ocx, float ocy, Dir h)
@@ -392,11 +396,13 @@ MBP_HD bool pair_maybe(float ocx, float ocy, Dir h)
 
 MBP_HD bool pair_candidates(float ocx, float ocy, Dir h, RaySpan &sp)
 {
-    if (!pair_maybe(ocx, ocy, h)) { sp.flo = sp.blo = 0; sp.fhi = sp.bhi = -1; return false; }
-    const RayCount rc = pair_spans(ocx, ocy, h);
-    sp.flo = rc.flo; sp.fhi = rc.flo + rc.cf - 1;
-    sp.blo = rc.blo; sp.bhi = rc.blo + rc.cb - 1;
-    return rc.cf + rc.cb > 0;
+    sp.flo = sp.blo = 0; sp.fhi = sp.bhi = -1;
+    if (!pair_maybe(ocx, ocy, h)) return false;
+    const RayRun rr = pair_run(ocx, ocy, h);
+    const int end = rr.lo + rr.count;                            /* exclusive */
+    if (rr.count > 0 && rr.lo < kFwdRays) { sp.flo = rr.lo; sp.fhi = (end < kFwdRays ? end : kFwdRays) - 1; }
+    if (rr.count > 0 && end > kFwdRays) { sp.blo = (rr.lo > kFwdRays ? rr.lo : kFwdRays) - kFwdRays; sp.bhi = end - 1 - kFwdRays; }
+    return rr.count > 0;
 }
 
 } // namespace mbp

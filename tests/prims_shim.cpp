@@ -125,7 +125,7 @@ long long shim_cull_trials(uint64_t seed, int trials, int n, int mode, long long
     return bad;
 }
 
-/* pair_maybe (stage 1 of the cull) must pass every pair for which pair_spans reports candidates. Random pairs
+/* pair_maybe (stage 1 of the cull) must pass every pair for which pair_run reports candidates. Random pairs
  * over the whole world plus pairs placed next to the wedge edges at every distance. Returns violations;
  * *passed = pairs that survive stage 1. */
 long long shim_wedge_trials(uint64_t seed, long long trials, long long *passed)
@@ -149,10 +149,10 @@ long long shim_wedge_trials(uint64_t seed, long long trials, long long *passed)
             ocx = -(cosf(edge) * dist - sinf(edge) * off);
             ocy = -(sinf(edge) * dist + cosf(edge) * off);
         }
-        const RayCount rc = pair_spans(ocx, ocy, h);
+        const RayRun rc = pair_run(ocx, ocy, h);
         const bool maybe = pair_maybe(ocx, ocy, h);
         if (maybe) ++*passed;
-        if ((rc.cf + rc.cb) > 0 && !maybe) ++bad;
+        if (rc.count > 0 && !maybe) ++bad;
     }
     return bad;
 }

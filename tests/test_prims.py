@@ -151,7 +151,7 @@ def test_culled_sensor_equals_exhaustive(S, mode, n, trials):
 
 
 def test_wedge_stage_never_rejects_a_pair_with_candidates(S):
-    """Stage 1 of the cull (pair_maybe) is conservative w.r.t. stage 2 (pair_spans), and rejects about half of
+    """Stage 1 of the cull (pair_maybe) is conservative w.r.t. stage 2 (pair_run), and rejects about half of
     uniformly random pairs."""
     passed = ctypes.c_longlong()
     n = 4_000_000
