@@ -180,6 +180,23 @@ int mbots_state_bytes(mbots_sim *sim, uint64_t *out);
 int mbots_save_state(mbots_sim *sim, void *host, uint64_t bytes, void *stream);
 int mbots_load_state(mbots_sim *sim, const void *host, uint64_t bytes, void *stream);
 
+/* Policy-inference ends, for callers that run the species networks on the
+ * exports. Rows [row_begin, row_end) of the CURRENT row set; both are asynchronous on `stream`.
+ *
+ * mbots_pack_observations: learn/util.py:23-29 construct_obs in one kernel -- writes the (n, 69) float32
+ *   matrix [depth u8 x32 | health | position x2 | semantic i8 x32 | surrounding x2] of the rows (is_prev
+ *   selects the prev_* exports) to the device buffer `out`.
+ * mbots_sample_actions: learn/training_loop.py:57,77-83,136 -- Categorical sample + one-hot write-back.
+ *   `weights` is a device (n, 6) float32 matrix of non-negative action weights (softmax of the logits; need
+ *   not be normalised). Row r draws u = uniform(split(split(init(seed), draw), row_begin + r)) with the
+ *   simulator's Threefry (M/include/madrona/rand.inl) and takes the first k with u * sum(w) < w0 + .. + wk
+ *   (sums in index order, fp32, no FMA), then stores the int32 one-hot row into the action export. The picked
+ *   index also goes to out_index[r] when that is not NULL. Deterministic in (seed, draw, row). */
+int mbots_pack_observations(mbots_sim *sim, int32_t is_prev, uint32_t row_begin, uint32_t row_end, float *out,
+                            void *stream);
+int mbots_sample_actions(mbots_sim *sim, uint32_t row_begin, uint32_t row_end, const float *weights, uint32_t seed,
+                         uint32_t draw, int32_t *out_index, void *stream);
+
 const char *mbots_last_error(void);
 const char *mbots_version(void);
 

@@ -615,3 +615,31 @@ int mbots_load_state(mbots_sim *s, const void *host, uint64_t bytes, void *strea
 }
 
 } /* extern "C" */
+
+/* ---- policy inference ends ---------------------------------------------------- */
+extern "C" {
+
+int mbots_pack_observations(mbots_sim *s, int32_t is_prev, uint32_t row_begin, uint32_t row_end, float *out, void *stream)
+{
+    if (!s || (!out && row_end > row_begin)) return fail(MBOTS_EINVAL, "null argument");
+    if (row_begin > row_end || row_end > s->totalAgents) return fail(MBOTS_EINVAL, "row range outside [0, num_agents]");
+    DeviceGuard g(s->device);
+    launch_pack_obs(s->d.obs[s->cur], is_prev != 0, row_begin, row_end - row_begin, out, (cudaStream_t)stream);
+    CU(cudaGetLastError());
+    s->launches += row_end > row_begin ? 1 : 0;
+    return MBOTS_OK;
+}
+
+int mbots_sample_actions(mbots_sim *s, uint32_t row_begin, uint32_t row_end, const float *weights, uint32_t seed,
+                         uint32_t draw, int32_t *out_index, void *stream)
+{
+    if (!s || (!weights && row_end > row_begin)) return fail(MBOTS_EINVAL, "null argument");
+    if (row_begin > row_end || row_end > s->totalAgents) return fail(MBOTS_EINVAL, "row range outside [0, num_agents]");
+    DeviceGuard g(s->device);
+    launch_sample(s->d.obs[s->cur], row_begin, row_end - row_begin, weights, seed, draw, out_index, (cudaStream_t)stream);
+    CU(cudaGetLastError());
+    s->launches += row_end > row_begin ? 1 : 0;
+    return MBOTS_OK;
+}
+
+} /* extern "C" */

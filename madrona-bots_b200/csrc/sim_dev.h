@@ -86,6 +86,10 @@ int launch_export(const SimDev &d, int cur, int with_sensors, uint32_t bound, cu
 void launch_shift(const SimDev &d, int cur, uint32_t rows_upper, cudaStream_t s);
 void launch_stats_reduce(const SimDev &d, long long *out16, cudaStream_t s);
 void launch_debug_gather(const SimDev &d, int what, void *out, cudaStream_t s);
+/* launchers (policy_kernels.cu) */
+void launch_pack_obs(const ObsSet &o, int is_prev, uint32_t row_begin, uint32_t rows, float *out, cudaStream_t s);
+void launch_sample(const ObsSet &o, uint32_t row_begin, uint32_t rows, const float *weights, uint32_t seed, uint32_t draw,
+                   int32_t *out_index, cudaStream_t s);
 size_t step_smem_bytes(uint32_t slots);
 size_t export_smem_bytes(uint32_t slots, uint32_t tile, bool fast);
 

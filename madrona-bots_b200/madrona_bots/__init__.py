@@ -214,6 +214,32 @@ class SimManager:
         _native.check(self._lib.mbots_copy_to_host(self._h, EXPORT[name], ctypes.c_void_p(host_ptr), nbytes,
                                                    self._stream()), "mbots_copy_to_host")
 
+    # ---- policy-inference ends --------------------------------
+    def pack_observations(self, start, end, prev=False, out=None):
+        """learn/util.py construct_obs(sim_mgr, start, end, prev) as one kernel: (end-start, 69) float32."""
+        import torch
+        n = int(end) - int(start)
+        if out is None:
+            out = torch.empty((n, 69), dtype=torch.float32, device=torch.device("cuda", self._gpu_id))
+        assert out.is_contiguous() and out.dtype == torch.float32 and out.shape == (n, 69)
+        _native.check(self._lib.mbots_pack_observations(self._h, 1 if prev else 0, int(start), int(end),
+                                                        ctypes.c_void_p(out.data_ptr()), self._stream()),
+                      "mbots_pack_observations")
+        return out
+
+    def sample_actions(self, start, end, weights, seed, draw, want_index=False):
+        """Categorical sample of rows [start, end) from (n, 6) float32 action weights + one-hot write into
+        the action export (training_loop.py:57,77-83,136). Returns the picked indices when asked to."""
+        import torch
+        n = int(end) - int(start)
+        assert weights.is_contiguous() and weights.dtype == torch.float32 and weights.shape == (n, 6)
+        idx = torch.empty(n, dtype=torch.int32, device=weights.device) if want_index else None
+        _native.check(self._lib.mbots_sample_actions(self._h, int(start), int(end), ctypes.c_void_p(weights.data_ptr()),
+                                                     int(seed) & 0xFFFFFFFF, int(draw) & 0xFFFFFFFF,
+                                                     ctypes.c_void_p(idx.data_ptr()) if want_index else None,
+                                                     self._stream()), "mbots_sample_actions")
+        return idx
+
     # ---- state checkpoint / restore (SURVEY section 8(f) item 3) ---------------------------
     def save_state(self, path=None):
         """Every persistent array of the simulator as one uint8 numpy blob (also written to `path`

@@ -24,7 +24,7 @@ SYMBOLS = [
     "mbots_shift_observations", "mbots_shift_observations_async", "mbots_num_agents", "mbots_tensor",
     "mbots_set_action", "mbots_agent_offset_for_world", "mbots_copy_from_host", "mbots_copy_to_host",
     "mbots_episode_stats", "mbots_launch_count", "mbots_profile", "mbots_profile_read",
-    "mbots_row_capacity", "mbots_state_bytes", "mbots_save_state", "mbots_load_state",
+    "mbots_row_capacity", "mbots_pack_observations", "mbots_sample_actions", "mbots_state_bytes", "mbots_save_state", "mbots_load_state",
     "mbots_last_error", "mbots_version",
 ]
 
@@ -64,6 +64,8 @@ def lib():
     L.mbots_launch_count.argtypes = [vp, ctypes.POINTER(u64)]
     L.mbots_profile.argtypes = [vp, i32]
     L.mbots_profile_read.argtypes = [vp, ctypes.POINTER(ctypes.c_float), ctypes.POINTER(u32)]
+    L.mbots_pack_observations.argtypes = [vp, i32, u32, u32, vp, vp]
+    L.mbots_sample_actions.argtypes = [vp, u32, u32, vp, u32, u32, vp, vp]
     L.mbots_row_capacity.argtypes = [vp, ctypes.POINTER(u64)]
     L.mbots_state_bytes.argtypes = [vp, ctypes.POINTER(u64)]
     L.mbots_save_state.argtypes = [vp, vp, u64, vp]

@@ -1,0 +1,140 @@
+"""Policy-inference ends on the GPU: the fused construct_obs kernel against torch.cat of the
+exports, the sampling kernel against a host restatement built on the same Threefry primitives, and a
+policy-in-the-loop rollout that stays bit-exact with the CPU oracle fed the same actions."""
+import ctypes
+
+import numpy as np
+import pytest
+
+from parity_util import compare, make_pair
+from test_policy import _make
+
+pytestmark = pytest.mark.gpu
+
+
+def _construct_obs(sim, start, end, prev):
+    """learn/util.py:23-29, verbatim in structure."""
+    import torch
+    return torch.cat((sim.depth_tensor(prev).to_torch()[start:end, :],
+                      sim.health_tensor(prev).to_torch()[start:end, :],
+                      sim.position_tensor(prev).to_torch()[start:end, :],
+                      sim.semantic_tensor(prev).to_torch()[start:end, :],
+                      sim.surrounding_tensor(prev).to_torch()[start:end, :]), dim=1)
+
+
+def _random_steps(sim, steps, seed):
+    import torch
+    g = torch.Generator(device="cuda").manual_seed(seed)
+    for _ in range(steps):
+        a = sim.action_tensor(False).to_torch()
+        a.zero_()
+        a.scatter_(1, torch.randint(0, 6, (a.shape[0], 1), generator=g, device="cuda"), 1)
+        sim.step()
+        sim.shift_observations()
+    sim.step()
+
+
+def test_pack_observations_equals_construct_obs(cuda_device):
+    import torch
+    from madrona_bots import SimManager
+    sim = SimManager(0, 40, 3, 32)
+    _random_steps(sim, 6, 1)
+    A = sim.num_agents()
+    for prev in (False, True):
+        for start, end in ((0, A), (17, A - 5), (A // 2, A // 2), (A - 1, A)):
+            got = sim.pack_observations(start, end, prev=prev)
+            want = _construct_obs(sim, start, end, prev).to(torch.float32)
+            assert got.shape == (end - start, 69) and got.dtype == torch.float32
+            assert torch.equal(got, want)
+    assert float(sim.pack_observations(0, A)[:, 35:67].min()) == -1.0       # a missed ray's semantic
+    with pytest.raises(RuntimeError, match="row range"):
+        sim.pack_observations(0, A + 1)
+
+
+def _host_sample(shim, weights, seed, draw, row_begin):
+    """The kernel's definition, restated on the host with the product's own Threefry (prims shim)."""
+    k0, k1, k2 = (ctypes.c_uint32 * 2)(), (ctypes.c_uint32 * 2)(), (ctypes.c_uint32 * 2)()
+    shim.shim_init_key(seed, k0)
+    shim.shim_split(k0[0], k0[1], draw, 0, k1)
+    out = np.empty(len(weights), dtype=np.int32)
+    f32 = np.float32
+    for r, w in enumerate(weights.astype(np.float32)):
+        shim.shim_split(k1[0], k1[1], row_begin + r, 0, k2)
+        u = f32(shim.shim_sample_uniform(k2[0], k2[1]))
+        total = w[0]
+        for k in range(1, 6):
+            total = f32(total + w[k])
+        thr, c, pick = f32(u * total), f32(0), 5
+        for k in range(6):
+            c = f32(c + w[k])
+            if thr < c:
+                pick = k
+                break
+        out[r] = pick
+    return out
+
+
+def test_sample_actions_matches_host_restatement(cuda_device):
+    import torch
+    from madrona_bots import SimManager
+    from prims_binding import shim
+    sim = SimManager(0, 24, 5, 32)
+    sim.step()
+    A = sim.num_agents()
+    start, end = 11, A - 7
+    g = torch.Generator(device="cuda").manual_seed(4)
+    w = torch.rand((end - start, 6), generator=g, device="cuda")
+    w[::7, 2] = 0.0                      # zero-weight actions must never be picked
+    w[5] = torch.tensor([0, 0, 0, 0, 0, 1.0])
+    before = sim.action_tensor(False).to_torch().clone()
+    idx = sim.sample_actions(start, end, w, seed=9, draw=3, want_index=True)
+    want = _host_sample(shim(), w.cpu().numpy(), 9, 3, start)
+    np.testing.assert_array_equal(idx.cpu().numpy(), want)
+    act = sim.action_tensor(False).to_torch()
+    assert torch.equal(act[start:end], torch.nn.functional.one_hot(idx.long(), 6).to(torch.int32))
+    assert torch.equal(act[:start], before[:start]) and torch.equal(act[end:], before[end:])
+    assert int(idx[5]) == 5 and not bool((idx[::7] == 2).any())
+    # another draw counter gives another sample; the same one repeats
+    idx2 = sim.sample_actions(start, end, w, seed=9, draw=4, want_index=True)
+    idx3 = sim.sample_actions(start, end, w, seed=9, draw=3, want_index=True)
+    assert not torch.equal(idx, idx2) and torch.equal(idx, idx3)
+    # the empirical distribution follows the weights
+    big = torch.tensor([[1.0, 2.0, 3.0, 4.0, 0.0, 10.0]], device="cuda").repeat(end - start, 1).contiguous()
+    hist = torch.zeros(6)
+    for d in range(40):
+        hist += torch.bincount(sim.sample_actions(start, end, big, 1, 100 + d, want_index=True).long().cpu(), minlength=6)
+    p = hist / hist.sum()
+    np.testing.assert_allclose(p.numpy(), np.array([1, 2, 3, 4, 0, 10]) / 20.0, atol=0.01)
+
+
+def test_policy_in_the_loop_rollout_matches_oracle(cuda_device):
+    """Species networks drive the simulation; the oracle is fed the sampled actions and must stay bit-identical."""
+    import torch
+    from madrona_bots.policy import PolicyRunner, SpeciesPolicy
+    torch.manual_seed(0)
+    pols = []
+    for rtype, acts in (("GRU", ["Tanh", "ReLU"]), ("LSTM", ["LeakyReLU", "ReLU"]), ("RNN", ["LogSigmoid", "Tanh", "ReLU"]),
+                        ("RNN", ["LogSigmoid", "Tanh", "LeakyReLU"])):          # the shapes of universe_violence
+        net, config = _make(rtype, acts)
+        pols.append(SpeciesPolicy(config, net.state_dict(), "cuda:0"))
+    o, g = make_pair(32, 6, 32)
+    o.step(); g.step()
+    runner = PolicyRunner(g, pols, seed=2)
+    picked_hist = torch.zeros(6)
+    for t in range(12):
+        blocks = runner.species_blocks()
+        assert blocks[0][0] == 0 and blocks[3][1] == g.num_agents() and all(a <= b for a, b in blocks)
+        sp = g.export("DEBUG_AGENT_SPECIES").to_torch()[:, 0].clone()
+        rows = g.sensor_index_tensor().to_torch()[:, 0].long()
+        by_row = torch.empty_like(sp); by_row[rows] = sp
+        for k, (a, b) in enumerate(blocks):
+            assert bool((by_row[a:b] == k + 1).all())
+        picked = runner.act(want_index=True)
+        act = g.action_tensor(False).to_torch()
+        assert bool((act.sum(dim=1) == 1).all())
+        picked_hist += torch.bincount(torch.cat([p for p in picked if p is not None]).long().cpu(), minlength=6)
+        o.tensor("ACTION")[:] = act.cpu().numpy()
+        o.step(); g.step()
+        compare(o, g, f"policy step {t}")
+        o.shift_observations(); g.shift_observations()
+    assert int((picked_hist > 0).sum()) >= 2
