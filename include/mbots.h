@@ -24,6 +24,7 @@
 #define MBOTS_H
 
 #include <stdint.h>
+#include "mbots_policy.h"
 
 #ifdef __cplusplus
 extern "C" {
@@ -196,6 +197,16 @@ int mbots_pack_observations(mbots_sim *sim, int32_t is_prev, uint32_t row_begin,
                             void *stream);
 int mbots_sample_actions(mbots_sim *sim, uint32_t row_begin, uint32_t row_end, const float *weights, uint32_t seed,
                          uint32_t draw, int32_t *out_index, void *stream);
+
+/* The whole acting path of learn/training_loop.py:52-83,136 for rows [row_begin, row_end) as ONE kernel:
+ * construct_obs -> species network (mbots_policy.h program over a device blob of bf16 weights) -> softmax ->
+ * Categorical sample (same stream as mbots_sample_actions: keyed seed, draw, row) -> one-hot row in the action
+ * export. Tensor-core products (bf16 in, fp32 accumulate); activations stay in registers between layers.
+ * sample = 0 skips sampling and the action write (use out_logits). out_logits: device (n, 6) float32 or NULL;
+ * out_index: device (n) int32 or NULL. Asynchronous on `stream`. MBOTS_EINVAL for a malformed program. */
+int mbots_policy_act(mbots_sim *sim, uint32_t row_begin, uint32_t row_end, const void *blob, uint64_t blob_bytes,
+                     const mbots_policy_program *program, uint32_t seed, uint32_t draw, int32_t sample,
+                     float *out_logits, int32_t *out_index, void *stream);
 
 const char *mbots_last_error(void);
 const char *mbots_version(void);

@@ -13,6 +13,7 @@
 #include <new>
 
 #include "../../include/mbots.h"
+#include "../../include/mbots_policy.h"
 #include "sim_dev.h"
 
 using namespace mbk;
@@ -643,3 +644,25 @@ int mbots_sample_actions(mbots_sim *s, uint32_t row_begin, uint32_t row_end, con
 }
 
 } /* extern "C" */
+
+/* ---- fused acting kernel (policy_fused.cu) ------------------------------------------------------------------ */
+namespace mbk {
+const char *launch_policy_fused(const ObsSet &o, uint32_t row_begin, uint32_t rows, const void *blob, uint64_t blob_bytes,
+                                const mbots_policy_program &prog, uint32_t seed, uint32_t draw, int do_sample,
+                                float *out_logits, int32_t *out_index, cudaStream_t s);
+}
+
+extern "C" int mbots_policy_act(mbots_sim *s, uint32_t row_begin, uint32_t row_end, const void *blob, uint64_t blob_bytes,
+                                const mbots_policy_program *program, uint32_t seed, uint32_t draw, int32_t sample,
+                                float *out_logits, int32_t *out_index, void *stream)
+{
+    if (!s || !blob || !program) return fail(MBOTS_EINVAL, "null argument");
+    if (row_begin > row_end || row_end > s->totalAgents) return fail(MBOTS_EINVAL, "row range outside [0, num_agents]");
+    DeviceGuard g(s->device);
+    const char *err = launch_policy_fused(s->d.obs[s->cur], row_begin, row_end - row_begin, blob, blob_bytes, *program, seed,
+                                          draw, sample != 0, out_logits, out_index, (cudaStream_t)stream);
+    if (err) return fail(MBOTS_EINVAL, err);
+    CU(cudaGetLastError());
+    s->launches += row_end > row_begin ? 1 : 0;
+    return MBOTS_OK;
+}

@@ -15,11 +15,10 @@
 #include <stdint.h>
 #include "sim_dev.h"
 #include "sim_prims.cuh"
+#include "policy_dev.cuh"
 
 namespace mbk {
 using namespace mbp;
-
-constexpr int kObsDim = 69;
 
 __global__ void __launch_bounds__(256) pack_obs_kernel(const uint8_t *__restrict__ depth, const float *__restrict__ health,
                                                        const float *__restrict__ position, const int8_t *__restrict__ semantic,
@@ -30,13 +29,7 @@ __global__ void __launch_bounds__(256) pack_obs_kernel(const uint8_t *__restrict
     for (size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x; idx < total; idx += (size_t)gridDim.x * blockDim.x) {
         const uint32_t r = (uint32_t)(idx / kObsDim), c = (uint32_t)(idx - (size_t)r * kObsDim);
         const size_t row = (size_t)row_begin + r;
-        float v;
-        if (c < 32u) v = (float)depth[row * 32 + c];
-        else if (c == 32u) v = health[row];
-        else if (c < 35u) v = position[row * 2 + (c - 33u)];
-        else if (c < 67u) v = (float)semantic[row * 32 + (c - 35u)];
-        else v = surrounding[row * 2 + (c - 67u)];
-        out[idx] = v;
+        out[idx] = obs_element(depth, health, position, semantic, surrounding, row, c);
     }
 }
 
@@ -52,24 +45,7 @@ __global__ void __launch_bounds__(256) sample_kernel(const float *__restrict__ w
     const float2 w01 = wp[0], w23 = wp[1], w45 = wp[2];
     const float w[6] = {w01.x, w01.y, w23.x, w23.y, w45.x, w45.y};
     const uint32_t row = row_begin + r;
-    const Key key = key_split(key_split(key_init(seed), draw), row);
-    const float u = key_sample_uniform(key);
-    float total = w[0];
-#pragma unroll
-    for (int k = 1; k < 6; ++k) total = total + w[k];
-    const float thr = u * total;
-    int pick = 5;
-    float c = 0.f;
-    bool done = false;
-#pragma unroll
-    for (int k = 0; k < 6; ++k) {
-        c = c + w[k];
-        if (!done && thr < c) { pick = k; done = true; }
-    }
-    int2 *ap = reinterpret_cast<int2 *>(action + (size_t)row * 6);
-    ap[0] = make_int2(pick == 0, pick == 1);
-    ap[1] = make_int2(pick == 2, pick == 3);
-    ap[2] = make_int2(pick == 4, pick == 5);
+    const int pick = sample_and_write(w, key_split(key_init(seed), draw), row, action);
     if (out_index) out_index[r] = pick;
 }
 

@@ -240,6 +240,23 @@ class SimManager:
                                                      self._stream()), "mbots_sample_actions")
         return idx
 
+    def policy_act(self, start, end, fused, seed, draw, sample=True, want_index=False, want_logits=False):
+        """One kernel: observations of rows [start, end) -> `fused` (madrona_bots.policy.FusedPolicy) -> sampled
+        one-hot actions in the action export. Returns the picked indices, the logits, both, or None."""
+        import torch
+        n = int(end) - int(start)
+        dev = torch.device("cuda", self._gpu_id)
+        idx = torch.empty(n, dtype=torch.int32, device=dev) if want_index else None
+        lg = torch.empty((n, 6), dtype=torch.float32, device=dev) if want_logits else None
+        _native.check(self._lib.mbots_policy_act(
+            self._h, int(start), int(end), ctypes.c_void_p(fused.blob.data_ptr()), fused.blob.numel(),
+            ctypes.byref(fused.program), int(seed) & 0xFFFFFFFF, int(draw) & 0xFFFFFFFF, 1 if sample else 0,
+            ctypes.c_void_p(lg.data_ptr()) if want_logits else None,
+            ctypes.c_void_p(idx.data_ptr()) if want_index else None, self._stream()), "mbots_policy_act")
+        if want_index and want_logits:
+            return idx, lg
+        return idx if want_index else lg
+
     # ---- state checkpoint / restore (SURVEY section 8(f) item 3) ---------------------------
     def save_state(self, path=None):
         """Every persistent array of the simulator as one uint8 numpy blob (also written to `path`

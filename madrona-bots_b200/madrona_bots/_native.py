@@ -24,9 +24,22 @@ SYMBOLS = [
     "mbots_shift_observations", "mbots_shift_observations_async", "mbots_num_agents", "mbots_tensor",
     "mbots_set_action", "mbots_agent_offset_for_world", "mbots_copy_from_host", "mbots_copy_to_host",
     "mbots_episode_stats", "mbots_launch_count", "mbots_profile", "mbots_profile_read",
-    "mbots_row_capacity", "mbots_pack_observations", "mbots_sample_actions", "mbots_state_bytes", "mbots_save_state", "mbots_load_state",
+    "mbots_row_capacity", "mbots_pack_observations", "mbots_sample_actions", "mbots_policy_act", "mbots_state_bytes", "mbots_save_state", "mbots_load_state",
     "mbots_last_error", "mbots_version",
 ]
+
+
+class PolicyOp(ctypes.Structure):          # mbots_policy_op (include/mbots_policy.h)
+    _fields_ = [("op", ctypes.c_int32), ("act", ctypes.c_int32), ("k_pad", ctypes.c_uint32),
+                ("w_ofs", ctypes.c_uint32), ("b_ofs", ctypes.c_uint32)]
+
+
+class PolicyProgram(ctypes.Structure):     # mbots_policy_program
+    _fields_ = [("n_ops", ctypes.c_int32), ("ops", PolicyOp * 12)]
+
+
+OP_LINEAR, OP_LSTM0, OP_GRU0, OP_HEAD = 0, 1, 2, 3
+ACT = dict(NONE=0, Tanh=1, ELU=2, LogSigmoid=3, LeakyReLU=4, ReLU=5, Sigmoid=6)
 
 
 class Config(ctypes.Structure):
@@ -66,6 +79,7 @@ def lib():
     L.mbots_profile_read.argtypes = [vp, ctypes.POINTER(ctypes.c_float), ctypes.POINTER(u32)]
     L.mbots_pack_observations.argtypes = [vp, i32, u32, u32, vp, vp]
     L.mbots_sample_actions.argtypes = [vp, u32, u32, vp, u32, u32, vp, vp]
+    L.mbots_policy_act.argtypes = [vp, u32, u32, vp, u64, ctypes.POINTER(PolicyProgram), u32, u32, i32, vp, vp, vp]
     L.mbots_row_capacity.argtypes = [vp, ctypes.POINTER(u64)]
     L.mbots_state_bytes.argtypes = [vp, ctypes.POINTER(u64)]
     L.mbots_save_state.argtypes = [vp, vp, u64, vp]

@@ -22,7 +22,7 @@ left untouched. Parity for this part is against torch's own modules (tests/test_
 import glob
 import os
 
-__all__ = ["SpeciesPolicy", "PolicyRunner", "load_universe"]
+__all__ = ["SpeciesPolicy", "FusedPolicy", "PolicyRunner", "load_universe"]
 
 _ACTIVATIONS = ("Tanh", "ELU", "LogSigmoid", "LeakyReLU", "ReLU")     # learn/models.py:63-69
 
@@ -46,11 +46,18 @@ def _act(name, x):
 class SpeciesPolicy:
     """One species' actor (and critic) from a reference checkpoint: inference only, fp32."""
 
-    def __init__(self, config, state_dict, device):
+    def __init__(self, config, state_dict, device, dtype="fp32"):
+        """dtype: "fp32" (default; matches torch's fp32 modules to 1e-5), "tf32" (fp32 storage, tensor-core
+        GEMMs) or "bf16" (weights and activations in bfloat16, fp32 accumulation, fp32 logits)."""
         import torch
+        if dtype not in ("fp32", "tf32", "bf16"):
+            raise ValueError("dtype must be fp32, tf32 or bf16")
         self.config = config
+        self.dtype = dtype
         self.device = torch.device(device)
-        sd = {k: v.detach().to(self.device, torch.float32).contiguous() for k, v in state_dict.items()}
+        wt = torch.bfloat16 if dtype == "bf16" else torch.float32
+        self._wt = wt
+        sd = {k: v.detach().to(self.device, wt).contiguous() for k, v in state_dict.items()}
         self.feature = self._stack(config["layers"], sd, "a2c_nets.feature")
         self.actor = self._stack(config["actor"], sd, "a2c_nets.actor")
         self.critic = self._stack(config["critic"], sd, "a2c_nets.critic")
@@ -110,26 +117,139 @@ class SpeciesPolicy:
         n = torch.tanh(g[:, 2 * H:] + self.b_in + rz[:, :H] * self.b_hn)
         return (1.0 - rz[:, H:]) * n
 
-    def forward(self, obs):
-        """(n, 69) float32 observations -> (logits (n, 6), value (n, 1))."""
+    def _ctx(self):
+        import contextlib
         import torch
-        with torch.no_grad():
-            shared = self.recurrent_step(self._run(self.feature, obs))
-            return self._run(self.actor, shared), self._run(self.critic, shared)
+        if self.dtype != "tf32":
+            return contextlib.nullcontext()
+
+        @contextlib.contextmanager
+        def tf32():
+            old = torch.backends.cuda.matmul.allow_tf32
+            torch.backends.cuda.matmul.allow_tf32 = True
+            try:
+                yield
+            finally:
+                torch.backends.cuda.matmul.allow_tf32 = old
+        return tf32()
+
+    def forward(self, obs):
+        """(n, 69) float32 observations -> (logits (n, 6), value (n, 1)), both float32."""
+        import torch
+        with torch.no_grad(), self._ctx():
+            shared = self.recurrent_step(self._run(self.feature, obs.to(self._wt)))
+            return self._run(self.actor, shared).float(), self._run(self.critic, shared).float()
 
     def logits(self, obs):
         import torch
-        with torch.no_grad():
-            return self._run(self.actor, self.recurrent_step(self._run(self.feature, obs)))
+        with torch.no_grad(), self._ctx():
+            return self._run(self.actor, self.recurrent_step(self._run(self.feature, obs.to(self._wt)))).float()
 
     @classmethod
-    def from_checkpoint(cls, path, device):
+    def from_checkpoint(cls, path, device, dtype="fp32"):
         import torch
         ck = torch.load(path, map_location="cpu", weights_only=False)
-        return cls(ck["model_config"], ck["model_state_dict"], device)
+        return cls(ck["model_config"], ck["model_state_dict"], device, dtype)
 
 
-def load_universe(base_dir, device, metric="latest", num_species=4):
+class FusedPolicy:
+    """A SpeciesPolicy compiled for `SimManager.policy_act` (libmbots.so `mbots_policy_act`): the network
+    flattened into the program + bf16 weight blob of include/mbots_policy.h, so that observation packing, every
+    layer, softmax, sampling and the action write run as ONE tensor-core kernel per species.
+    Restrictions of the kernel: hidden width 128, observation width 69, 6 actions (the reference's defaults,
+    learn/training_loop.py:228-232) and the actor head Linear-ReLU-Linear of learn/models.py:33-37."""
+
+    def __init__(self, policy):
+        import numpy as np
+        import torch
+        from . import _native
+        H, PAD = 128, 8
+        if policy.hidden_dim != H:
+            raise ValueError("the fused kernel is built for hidden_dim 128")
+        chunks, size = [], 0
+
+        def put(arr):
+            nonlocal size
+            ofs = size
+            raw = arr.tobytes()
+            raw += b"\0" * (-len(raw) % 16)
+            chunks.append(raw)
+            size += len(raw)
+            return ofs
+
+        def bf16_bits(t):      # (rows, k) float tensor -> uint16 bit patterns, round to nearest even
+            return t.to(torch.bfloat16).view(torch.int16).cpu().numpy().view(np.uint16)
+
+        def block(w, rows, k_pad):     # w: (out, in) -> [rows][k_pad + 8] bf16, zero padded
+            out = np.zeros((rows, k_pad + PAD), dtype=np.uint16)
+            out[: w.shape[0], : w.shape[1]] = bf16_bits(w)
+            return out
+
+        def f32(t):
+            return t.detach().float().cpu().numpy().astype(np.float32)
+
+        ops = []
+
+        def linear(w_t, b, act, first):
+            w = w_t.t().float()                         # stored transposed in SpeciesPolicy
+            k_pad = 80 if first else H
+            if w.shape[0] != H or w.shape[1] > k_pad or (not first and w.shape[1] != H):
+                raise ValueError("the fused kernel needs 69 -> 128 -> ... -> 128 linear layers")
+            ops.append((_native.OP_LINEAR, act, k_pad, put(block(w, H, k_pad)), put(f32(b))))
+
+        def stack(layers, first):
+            i = 0
+            while i < len(layers):
+                kind = layers[i]
+                if kind[0] != "linear":
+                    raise ValueError("an activation without a preceding linear layer")
+                act = "NONE"
+                if i + 1 < len(layers) and layers[i + 1][0] == "act":
+                    act = layers[i + 1][1]
+                    i += 1
+                if i + 1 < len(layers) and layers[i + 1][0] == "act":
+                    raise ValueError("two activations in a row")
+                linear(kind[1], kind[2], _native.ACT[act], first)
+                first = False
+                i += 1
+
+        stack(policy.feature, True)
+        w_ih = policy.w_ih_t.t().float()                # (gates * H, H)
+        if w_ih.shape[1] != H:
+            raise ValueError("recurrent input width must be 128")
+        if policy.rtype == "RNN":
+            ops.append((_native.OP_LINEAR, _native.ACT["Tanh"], H, put(block(w_ih, H, H)), put(f32(policy.b))))
+        elif policy.rtype == "LSTM":                    # torch gate order i, f, g, o; f is unused from c0 = 0
+            b = policy.b.float()
+            w_ofs = put(np.concatenate([block(w_ih[j * H:(j + 1) * H], H, H) for j in (0, 2, 3)]))
+            ops.append((_native.OP_LSTM0, 0, H, w_ofs, put(np.concatenate([f32(b[j * H:(j + 1) * H]) for j in (0, 2, 3)]))))
+        else:                                           # GRU: r, z, n
+            w_ofs = put(np.concatenate([block(w_ih[j * H:(j + 1) * H], H, H) for j in range(3)]))
+            b_rz = policy.b_rz.float()
+            ops.append((_native.OP_GRU0, 0, H, w_ofs,
+                        put(np.concatenate([f32(b_rz[:H]), f32(b_rz[H:]), f32(policy.b_in), f32(policy.b_hn)]))))
+        actor = policy.actor
+        if [l[0] for l in actor] != ["linear", "act", "linear"] or actor[1][1] != "ReLU":
+            raise ValueError("actor head must be Linear-ReLU-Linear")
+        linear(actor[0][1], actor[0][2], _native.ACT["ReLU"], False)
+        w_out, b_out = actor[2][1].t().float(), actor[2][2]
+        if w_out.shape != (6, H):
+            raise ValueError("the head must map 128 -> 6")
+        bias8 = np.zeros(8, dtype=np.float32)
+        bias8[:6] = f32(b_out)
+        ops.append((_native.OP_HEAD, 0, H, put(block(w_out, 8, H)), put(bias8)))
+        if len(ops) > 12:
+            raise ValueError("network too deep for the fused kernel (12 ops)")
+        self.program = _native.PolicyProgram()
+        self.program.n_ops = len(ops)
+        for i, (op, act, k_pad, w_ofs, b_ofs) in enumerate(ops):
+            self.program.ops[i] = _native.PolicyOp(op, act, k_pad, w_ofs, b_ofs)
+        host = np.frombuffer(b"".join(chunks), dtype=np.uint8).copy()
+        self.blob = torch.from_numpy(host).to(policy.device)
+        self.policy = policy
+
+
+def load_universe(base_dir, device, metric="latest", num_species=4, dtype="fp32"):
     """checkpoints/universe_<id>/species_<k>/{latest_model,best_<metric>}_epoch_<n>.pt -> [SpeciesPolicy] * 4,
     picking the highest epoch as learn/ckpt.py:36-48 does."""
     out = []
@@ -139,7 +259,7 @@ def load_universe(base_dir, device, metric="latest", num_species=4):
         if not files:
             raise FileNotFoundError(f"no {pat} under {base_dir}/species_{k}")
         files.sort(key=lambda p: int(p.split("_")[-1].split(".")[0]), reverse=True)
-        out.append(SpeciesPolicy.from_checkpoint(files[0], device))
+        out.append(SpeciesPolicy.from_checkpoint(files[0], device, dtype))
     return out
 
 
@@ -155,10 +275,13 @@ class PolicyRunner:
     Sampling is deterministic in (seed, act() call number, row): the same rollout replays bit-exactly.
     """
 
-    def __init__(self, sim, policies, seed=0):
+    def __init__(self, sim, policies, seed=0, fused=False):
+        """fused=True: each species acts through one `mbots_policy_act` kernel (bf16 tensor cores) instead of
+        pack kernel + library GEMMs + sample kernel."""
         if len(policies) != 4:
             raise ValueError("one policy per species (4)")
         self.sim, self.policies, self.seed = sim, policies, int(seed)
+        self.fused = [FusedPolicy(p) if not isinstance(p, FusedPolicy) else p for p in policies] if fused else None
         self.draw = 0
 
     def species_blocks(self):
@@ -171,9 +294,12 @@ class PolicyRunner:
     def act(self, want_index=False):
         import torch
         picked = []
-        for (start, end), pol in zip(self.species_blocks(), self.policies):
+        for k, ((start, end), pol) in enumerate(zip(self.species_blocks(), self.policies)):
             if end <= start:
                 picked.append(None)
+                continue
+            if self.fused is not None:
+                picked.append(self.sim.policy_act(start, end, self.fused[k], self.seed, self.draw, want_index=want_index))
                 continue
             obs = self.sim.pack_observations(start, end, prev=False)
             weights = torch.softmax(pol.logits(obs), dim=1).contiguous()

@@ -138,3 +138,108 @@ def test_policy_in_the_loop_rollout_matches_oracle(cuda_device):
         compare(o, g, f"policy step {t}")
         o.shift_observations(); g.shift_observations()
     assert int((picked_hist > 0).sum()) >= 2
+
+
+def _bf16_reference_logits(pol, obs):
+    """The fused kernel's arithmetic restated with torch: bf16 weights and layer inputs, fp32 accumulation,
+    fp32 bias / activation, GRU helper terms rounded to bf16 as the kernel keeps them."""
+    import torch
+    import torch.nn.functional as F
+    r = lambda t: t.to(torch.bfloat16).float()  # noqa: E731
+    acts = {"Tanh": torch.tanh, "ELU": F.elu, "LogSigmoid": F.logsigmoid, "LeakyReLU": F.leaky_relu, "ReLU": F.relu}
+
+    def run(stack, x):
+        for layer in stack:
+            x = r(x) @ r(layer[1].float()) + layer[2].float() if layer[0] == "linear" else acts[layer[1]](x)
+        return x
+    H = pol.hidden_dim
+    x = run(pol.feature, obs)
+    g = r(x) @ r(pol.w_ih_t.float())
+    if pol.rtype == "RNN":
+        h = torch.tanh(g + pol.b)
+    elif pol.rtype == "LSTM":
+        g = g + pol.b
+        h = torch.sigmoid(g[:, 3 * H:]) * torch.tanh(torch.sigmoid(g[:, :H]) * torch.tanh(g[:, 2 * H:3 * H]))
+    else:
+        rz = torch.sigmoid(g[:, :2 * H] + pol.b_rz)
+        h = r(1.0 - rz[:, H:]) * torch.tanh(g[:, 2 * H:] + pol.b_in + r(rz[:, :H] * pol.b_hn))
+    return run(pol.actor, h)
+
+
+@pytest.mark.parametrize("rtype,acts", [("GRU", ["Tanh", "ReLU"]), ("LSTM", ["LeakyReLU", "ReLU"]),
+                                        ("RNN", ["LogSigmoid", "Tanh", "ELU"])])
+def test_fused_policy_kernel_matches_its_restatement(cuda_device, rtype, acts):
+    import torch
+    from madrona_bots import SimManager
+    from madrona_bots.policy import FusedPolicy, SpeciesPolicy
+    from prims_binding import shim
+    torch.manual_seed(11)
+    net, config = _make(rtype, acts)
+    with torch.no_grad():                           # livelier logits than the default initialisation gives
+        for p in net.parameters():
+            p.mul_(2.0)
+    pol = SpeciesPolicy(config, net.state_dict(), "cuda:0")
+    fused = FusedPolicy(pol)
+    sim = SimManager(0, 40, 3, 32)
+    _random_steps(sim, 5, 2)
+    A = sim.num_agents()
+    for start, end in ((0, A), (3, 3 + 129), (A - 77, A), (10, 11)):
+        before = sim.action_tensor(False).to_torch().clone()
+        idx, lg = sim.policy_act(start, end, fused, seed=5, draw=8, want_index=True, want_logits=True)
+        ref = _bf16_reference_logits(pol, sim.pack_observations(start, end))
+        scale = float(ref.abs().max())
+        assert float((lg - ref).abs().max()) <= 3e-2 * scale + 1e-3, (float((lg - ref).abs().max()), scale)
+        assert float((lg - ref).abs().mean()) <= 3e-3 * scale + 1e-4
+        # and it is close to the fp32 network too (bf16 inputs: ~1e-2 relative)
+        full = pol.logits(sim.pack_observations(start, end))
+        assert float((lg - full).abs().max()) <= 0.3 * float(full.abs().max()) + 1e-2
+        # sampling: the kernel's own logits -> softmax weights -> the documented inverse-CDF draw
+        l = lg.cpu().numpy().astype(np.float32)
+        w = np.exp((l - l.max(axis=1, keepdims=True)).astype(np.float32)).astype(np.float32)
+        want = _host_sample(shim(), w, 5, 8, start)
+        assert int((idx.cpu().numpy() != want).sum()) <= max(1, (end - start) // 500)
+        act = sim.action_tensor(False).to_torch()
+        assert torch.equal(act[start:end], torch.nn.functional.one_hot(idx.long(), 6).to(torch.int32))
+        assert torch.equal(act[:start], before[:start]) and torch.equal(act[end:], before[end:])
+    # sample = 0 leaves the actions alone
+    before = sim.action_tensor(False).to_torch().clone()
+    sim.policy_act(0, A, fused, 1, 1, sample=False, want_logits=True)
+    assert torch.equal(sim.action_tensor(False).to_torch(), before)
+
+
+def test_fused_policy_rejects_malformed_programs(cuda_device):
+    import torch
+    from madrona_bots import SimManager
+    from madrona_bots.policy import FusedPolicy, SpeciesPolicy
+    net, config = _make("RNN", ["Tanh"])
+    fused = FusedPolicy(SpeciesPolicy(config, net.state_dict(), "cuda:0"))
+    sim = SimManager(0, 4, 0, 32)
+    sim.step()
+    fused.program.ops[fused.program.n_ops - 1].w_ofs = fused.blob.numel()        # beyond the blob
+    with pytest.raises(RuntimeError, match="beyond the blob"):
+        sim.policy_act(0, 8, fused, 0, 0)
+    fused.program.n_ops = 1
+    with pytest.raises(RuntimeError, match="2..12 ops"):
+        sim.policy_act(0, 8, fused, 0, 0)
+
+
+def test_fused_policy_in_the_loop_matches_oracle(cuda_device):
+    import torch
+    from madrona_bots.policy import PolicyRunner, SpeciesPolicy
+    torch.manual_seed(1)
+    pols = []
+    for rtype, acts in (("GRU", ["Tanh", "ReLU"]), ("LSTM", ["LeakyReLU", "ReLU"]), ("RNN", ["LogSigmoid", "Tanh", "ReLU"]),
+                        ("RNN", ["LogSigmoid", "Tanh", "LeakyReLU"])):
+        net, config = _make(rtype, acts)
+        pols.append(SpeciesPolicy(config, net.state_dict(), "cuda:0"))
+    o, g = make_pair(32, 8, 32)
+    o.step(); g.step()
+    runner = PolicyRunner(g, pols, seed=4, fused=True)
+    for t in range(10):
+        runner.act()
+        act = g.action_tensor(False).to_torch()
+        assert bool((act.sum(dim=1) == 1).all())
+        o.tensor("ACTION")[:] = act.cpu().numpy()
+        o.step(); g.step()
+        compare(o, g, f"fused policy step {t}")
+        o.shift_observations(); g.shift_observations()

@@ -25,9 +25,11 @@ def main():
     ap.add_argument("--steps", type=int, default=50)
     ap.add_argument("--warmup", type=int, default=10)
     ap.add_argument("--universe", default=None)
+    ap.add_argument("--dtype", default="fp32", choices=["fp32", "tf32", "bf16"])
+    ap.add_argument("--fused", action="store_true", help="one tensor-core kernel per species (mbots_policy_act)")
     a = ap.parse_args()
     if a.universe:
-        pols = load_universe(a.universe, "cuda:0")
+        pols = load_universe(a.universe, "cuda:0", dtype=a.dtype)
     else:
         from test_policy import _make
         torch.manual_seed(0)
@@ -35,9 +37,9 @@ def main():
         for rtype, acts in (("GRU", ["Tanh", "ReLU"]), ("LSTM", ["LeakyReLU", "ReLU"]),
                             ("RNN", ["LogSigmoid", "Tanh", "ReLU"]), ("RNN", ["LogSigmoid", "Tanh", "LeakyReLU"])):
             net, cfg = _make(rtype, acts)
-            pols.append(SpeciesPolicy(cfg, net.state_dict(), "cuda:0"))
+            pols.append(SpeciesPolicy(cfg, net.state_dict(), "cuda:0", a.dtype))
     sim = SimManager(0, a.worlds, 0, 32)
-    runner = PolicyRunner(sim, pols, seed=0)
+    runner = PolicyRunner(sim, pols, seed=0, fused=a.fused)
     ev = [torch.cuda.Event(enable_timing=True) for _ in range(4)]
     t_sim = t_pol = 0.0
     agent_steps = 0
@@ -57,7 +59,7 @@ def main():
     out = {"worlds": a.worlds, "steps": a.steps, "agents": sim.num_agents(),
            "sim_ms_per_step": t_sim / a.steps, "policy_ms_per_step": t_pol / a.steps,
            "agent_steps_per_s": agent_steps / ((t_sim + t_pol) * 1e-3),
-           "policy": "universe_violence architectures, " + ("loaded" if a.universe else "random weights") + ", fp32"}
+           "policy": "universe_violence architectures, " + ("loaded" if a.universe else "random weights") + ", " + ("fused bf16 kernel" if a.fused else a.dtype)}
     print(json.dumps(out))
 
 
