@@ -65,7 +65,6 @@ __device__ __forceinline__ float tanh_fast(float x)
     return y;
 }
 __device__ __forceinline__ float sigmoidf_(float x) { return fmaf(0.5f, tanh_fast(0.5f * x), 0.5f); }
-#define tanhf_ tanh_fast
 
 __device__ __forceinline__ float activate(int act, float x)
 {
@@ -111,10 +110,23 @@ __device__ __forceinline__ void repack(uint32_t (&a)[8][4], const float (&v)[16]
     }
 }
 
+template <int ACT>
+__device__ __forceinline__ void linear_epilogue(float (&acc)[16][4], const unsigned char *__restrict__ bias, int q)
+{
+#pragma unroll
+    for (int nt = 0; nt < 16; ++nt) {
+        const float2 bb = __ldg(reinterpret_cast<const float2 *>(bias) + nt * 4 + q);
+        acc[nt][0] = activate(ACT, acc[nt][0] + bb.x); acc[nt][1] = activate(ACT, acc[nt][1] + bb.y);
+        acc[nt][2] = activate(ACT, acc[nt][2] + bb.x); acc[nt][3] = activate(ACT, acc[nt][3] + bb.y);
+    }
+}
+
 struct FusedPlan {                        /* weight blocks in streaming order */
     int32_t n_blocks;
     uint32_t ofs[3 * MBOTS_POLICY_MAX_OPS];
     uint32_t bytes[3 * MBOTS_POLICY_MAX_OPS];
+    uint8_t op_of[3 * MBOTS_POLICY_MAX_OPS];      /* op a block belongs to */
+    uint8_t gate_of[3 * MBOTS_POLICY_MAX_OPS];    /* its index within that op (recurrent gates) */
 };
 
 struct ObsPtrs { const uint8_t *depth; const float *health; const float *position; const int8_t *semantic; const float *surrounding; };
@@ -190,129 +202,133 @@ policy_fused_kernel(ObsPtrs o, int32_t *__restrict__ action, uint32_t row_begin,
             }
         }
 
+        /* One pass per weight block: product, then the epilogue that block's (op, gate) asks for. Two product
+         * instantiations in the whole kernel (K = 80 and K = 128) keep the code inside the instruction cache. */
         uint32_t a[8][4];
         float acc[16][4];
-        int b = 0;
-        for (int oi = 0; oi < prog.n_ops; ++oi) {
-            const mbots_policy_op op = prog.ops[oi];
+        float keep[16][4];      /* LSTM: sigmoid(i), then c. GRU: [0..1] = r * b_hn, [2..3] = 1 - z, as packed bf16 pairs */
+#pragma unroll 1
+        for (int b = 0; b < plan.n_blocks - 1; ++b) {
+            const mbots_policy_op op = prog.ops[plan.op_of[b]];
+            const int gate = plan.gate_of[b];
+            const uint32_t w = acquire_block(b);
+            if (b == 0) {
+                /* first block: A fragments from the observation tile */
+                const uint32_t row_addr = obs_base + (uint32_t)(warp * 16 + (lane & 7) + ((lane >> 3) & 1) * 8) * ((kObsK + kPadK) * 2) +
+                                          (uint32_t)(lane >> 4) * 16u;
+#pragma unroll
+                for (int ks = 0; ks < kObsK / 16; ++ks) ldmatrix_x4(a[ks], row_addr + (uint32_t)ks * 32u);
+                gemm_block<kObsK / 16>(acc, a, w, (kObsK + kPadK) * 2);
+            } else {
+                gemm_block<kHid / 16>(acc, a, w, (kHid + kPadK) * 2);
+            }
             if (op.op == MBOTS_OP_LINEAR) {
-                const uint32_t w = acquire_block(b++);
-                if (op.k_pad == (uint32_t)kObsK) {
-                    /* first block: A fragments from the observation tile */
-                    const uint32_t row_addr = obs_base + (uint32_t)(warp * 16 + (lane & 7) + ((lane >> 3) & 1) * 8) * ((kObsK + kPadK) * 2) +
-                                              (uint32_t)(lane >> 4) * 16u;
-#pragma unroll
-                    for (int ks = 0; ks < kObsK / 16; ++ks) ldmatrix_x4(a[ks], row_addr + (uint32_t)ks * 32u);
-                    gemm_block<kObsK / 16>(acc, a, w, (kObsK + kPadK) * 2);
-                } else {
-                    gemm_block<kHid / 16>(acc, a, w, (kHid + kPadK) * 2);
-                }
-#pragma unroll
-                for (int nt = 0; nt < 16; ++nt) {
-                    const float2 bb = bias2(op.b_ofs, 0, nt);
-                    acc[nt][0] = activate(op.act, acc[nt][0] + bb.x); acc[nt][1] = activate(op.act, acc[nt][1] + bb.y);
-                    acc[nt][2] = activate(op.act, acc[nt][2] + bb.x); acc[nt][3] = activate(op.act, acc[nt][3] + bb.y);
+                switch (op.act) {
+                case MBOTS_ACT_TANH: linear_epilogue<MBOTS_ACT_TANH>(acc, blob + op.b_ofs, q); break;
+                case MBOTS_ACT_ELU: linear_epilogue<MBOTS_ACT_ELU>(acc, blob + op.b_ofs, q); break;
+                case MBOTS_ACT_LOGSIGMOID: linear_epilogue<MBOTS_ACT_LOGSIGMOID>(acc, blob + op.b_ofs, q); break;
+                case MBOTS_ACT_LEAKYRELU: linear_epilogue<MBOTS_ACT_LEAKYRELU>(acc, blob + op.b_ofs, q); break;
+                case MBOTS_ACT_RELU: linear_epilogue<MBOTS_ACT_RELU>(acc, blob + op.b_ofs, q); break;
+                case MBOTS_ACT_SIGMOID: linear_epilogue<MBOTS_ACT_SIGMOID>(acc, blob + op.b_ofs, q); break;
+                default: linear_epilogue<MBOTS_ACT_NONE>(acc, blob + op.b_ofs, q); break;
                 }
                 repack(a, acc);
             } else if (op.op == MBOTS_OP_LSTM0) {
-                float keep[16][4];
-                uint32_t w = acquire_block(b++);                      /* i gate */
-                gemm_block<kHid / 16>(acc, a, w, (kHid + kPadK) * 2);
+                if (gate == 0) {                                      /* i gate */
 #pragma unroll
-                for (int nt = 0; nt < 16; ++nt) {
-                    const float2 bb = bias2(op.b_ofs, 0, nt);
-                    keep[nt][0] = sigmoidf_(acc[nt][0] + bb.x); keep[nt][1] = sigmoidf_(acc[nt][1] + bb.y);
-                    keep[nt][2] = sigmoidf_(acc[nt][2] + bb.x); keep[nt][3] = sigmoidf_(acc[nt][3] + bb.y);
+                    for (int nt = 0; nt < 16; ++nt) {
+                        const float2 bb = bias2(op.b_ofs, 0, nt);
+                        keep[nt][0] = sigmoidf_(acc[nt][0] + bb.x); keep[nt][1] = sigmoidf_(acc[nt][1] + bb.y);
+                        keep[nt][2] = sigmoidf_(acc[nt][2] + bb.x); keep[nt][3] = sigmoidf_(acc[nt][3] + bb.y);
+                    }
+                } else if (gate == 1) {                               /* g gate: c = sigmoid(i) * tanh(g) */
+#pragma unroll
+                    for (int nt = 0; nt < 16; ++nt) {
+                        const float2 bb = bias2(op.b_ofs, 1, nt);
+                        keep[nt][0] *= tanh_fast(acc[nt][0] + bb.x); keep[nt][1] *= tanh_fast(acc[nt][1] + bb.y);
+                        keep[nt][2] *= tanh_fast(acc[nt][2] + bb.x); keep[nt][3] *= tanh_fast(acc[nt][3] + bb.y);
+                    }
+                } else {                                              /* o gate: h = sigmoid(o) * tanh(c) */
+#pragma unroll
+                    for (int nt = 0; nt < 16; ++nt) {
+                        const float2 bb = bias2(op.b_ofs, 2, nt);
+                        acc[nt][0] = sigmoidf_(acc[nt][0] + bb.x) * tanh_fast(keep[nt][0]); acc[nt][1] = sigmoidf_(acc[nt][1] + bb.y) * tanh_fast(keep[nt][1]);
+                        acc[nt][2] = sigmoidf_(acc[nt][2] + bb.x) * tanh_fast(keep[nt][2]); acc[nt][3] = sigmoidf_(acc[nt][3] + bb.y) * tanh_fast(keep[nt][3]);
+                    }
+                    repack(a, acc);
                 }
-                w = acquire_block(b++);                               /* g gate: c = sigmoid(i) * tanh(g) */
-                gemm_block<kHid / 16>(acc, a, w, (kHid + kPadK) * 2);
+            } else {                                                  /* GRU0 */
+                if (gate == 0) {                                      /* r gate */
 #pragma unroll
-                for (int nt = 0; nt < 16; ++nt) {
-                    const float2 bb = bias2(op.b_ofs, 1, nt);
-                    keep[nt][0] *= tanhf_(acc[nt][0] + bb.x); keep[nt][1] *= tanhf_(acc[nt][1] + bb.y);
-                    keep[nt][2] *= tanhf_(acc[nt][2] + bb.x); keep[nt][3] *= tanhf_(acc[nt][3] + bb.y);
+                    for (int nt = 0; nt < 16; ++nt) {
+                        const float2 bb = bias2(op.b_ofs, 0, nt), hn = bias2(op.b_ofs, 3, nt);
+                        keep[nt][0] = __uint_as_float(pack_bf16(sigmoidf_(acc[nt][0] + bb.x) * hn.x, sigmoidf_(acc[nt][1] + bb.y) * hn.y));
+                        keep[nt][1] = __uint_as_float(pack_bf16(sigmoidf_(acc[nt][2] + bb.x) * hn.x, sigmoidf_(acc[nt][3] + bb.y) * hn.y));
+                    }
+                } else if (gate == 1) {                               /* z gate */
+#pragma unroll
+                    for (int nt = 0; nt < 16; ++nt) {
+                        const float2 bb = bias2(op.b_ofs, 1, nt);
+                        keep[nt][2] = __uint_as_float(pack_bf16(1.f - sigmoidf_(acc[nt][0] + bb.x), 1.f - sigmoidf_(acc[nt][1] + bb.y)));
+                        keep[nt][3] = __uint_as_float(pack_bf16(1.f - sigmoidf_(acc[nt][2] + bb.x), 1.f - sigmoidf_(acc[nt][3] + bb.y)));
+                    }
+                } else {                                              /* n gate: h = (1 - z) * tanh(n + b_in + r * b_hn) */
+#pragma unroll
+                    for (int nt = 0; nt < 16; ++nt) {
+                        const float2 bb = bias2(op.b_ofs, 2, nt);
+                        const float2 r0 = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162 *>(&keep[nt][0]));
+                        const float2 r1 = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162 *>(&keep[nt][1]));
+                        const float2 z0 = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162 *>(&keep[nt][2]));
+                        const float2 z1 = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162 *>(&keep[nt][3]));
+                        acc[nt][0] = z0.x * tanh_fast(acc[nt][0] + bb.x + r0.x); acc[nt][1] = z0.y * tanh_fast(acc[nt][1] + bb.y + r0.y);
+                        acc[nt][2] = z1.x * tanh_fast(acc[nt][2] + bb.x + r1.x); acc[nt][3] = z1.y * tanh_fast(acc[nt][3] + bb.y + r1.y);
+                    }
+                    repack(a, acc);
                 }
-                w = acquire_block(b++);                               /* o gate: h = sigmoid(o) * tanh(c) */
-                gemm_block<kHid / 16>(acc, a, w, (kHid + kPadK) * 2);
+            }
+        }
+        {                                                             /* HEAD: 8 output rows, one n-tile */
+            const int b = plan.n_blocks - 1;
+            const mbots_policy_op op = prog.ops[prog.n_ops - 1];
+            const uint32_t w = acquire_block(b);
+            float lg[4] = {0.f, 0.f, 0.f, 0.f};
+            const uint32_t lane_addr = w + (uint32_t)(lane & 7) * ((kHid + kPadK) * 2) + (uint32_t)(lane >> 3) * 16u;
 #pragma unroll
-                for (int nt = 0; nt < 16; ++nt) {
-                    const float2 bb = bias2(op.b_ofs, 2, nt);
-                    acc[nt][0] = sigmoidf_(acc[nt][0] + bb.x) * tanhf_(keep[nt][0]); acc[nt][1] = sigmoidf_(acc[nt][1] + bb.y) * tanhf_(keep[nt][1]);
-                    acc[nt][2] = sigmoidf_(acc[nt][2] + bb.x) * tanhf_(keep[nt][2]); acc[nt][3] = sigmoidf_(acc[nt][3] + bb.y) * tanhf_(keep[nt][3]);
-                }
-                repack(a, acc);
-            } else if (op.op == MBOTS_OP_GRU0) {
-                uint32_t rb[16][2], omz[16][2];                       /* r * b_hn and 1 - z, packed bf16 pairs */
-                uint32_t w = acquire_block(b++);                      /* r gate */
-                gemm_block<kHid / 16>(acc, a, w, (kHid + kPadK) * 2);
+            for (int kp = 0; kp < kHid / 32; ++kp) {                  /* two k-steps per ldmatrix.x4 */
+                uint32_t bf[4];
+                ldmatrix_x4(bf, lane_addr + (uint32_t)kp * 64u);
+                mma_bf16(lg, a[2 * kp], bf[0], bf[1]);
+                mma_bf16(lg, a[2 * kp + 1], bf[2], bf[3]);
+            }
+            const float2 bb = __ldg(reinterpret_cast<const float2 *>(blob + op.b_ofs) + q);
+            lg[0] += bb.x; lg[1] += bb.y; lg[2] += bb.x; lg[3] += bb.y;
+            /* the 8 logits of a row sit in the 4 lanes of a quad: lane q = 0 takes row g, lane q = 1 row g + 8 */
+            float l0[8], l1[8];
 #pragma unroll
-                for (int nt = 0; nt < 16; ++nt) {
-                    const float2 bb = bias2(op.b_ofs, 0, nt), hn = bias2(op.b_ofs, 3, nt);
-                    rb[nt][0] = pack_bf16(sigmoidf_(acc[nt][0] + bb.x) * hn.x, sigmoidf_(acc[nt][1] + bb.y) * hn.y);
-                    rb[nt][1] = pack_bf16(sigmoidf_(acc[nt][2] + bb.x) * hn.x, sigmoidf_(acc[nt][3] + bb.y) * hn.y);
-                }
-                w = acquire_block(b++);                               /* z gate */
-                gemm_block<kHid / 16>(acc, a, w, (kHid + kPadK) * 2);
+            for (int j = 0; j < 4; ++j) {
+                const int src = (lane & ~3) + j;
+                l0[2 * j] = __shfl_sync(0xffffffffu, lg[0], src); l0[2 * j + 1] = __shfl_sync(0xffffffffu, lg[1], src);
+                l1[2 * j] = __shfl_sync(0xffffffffu, lg[2], src); l1[2 * j + 1] = __shfl_sync(0xffffffffu, lg[3], src);
+            }
+            if (q < 2) {
+                const size_t lr = (size_t)tile * kTileRows + warp * 16 + g + (q ? 8 : 0);
+                if (lr < rows) {
+                    float l[6];
 #pragma unroll
-                for (int nt = 0; nt < 16; ++nt) {
-                    const float2 bb = bias2(op.b_ofs, 1, nt);
-                    omz[nt][0] = pack_bf16(1.f - sigmoidf_(acc[nt][0] + bb.x), 1.f - sigmoidf_(acc[nt][1] + bb.y));
-                    omz[nt][1] = pack_bf16(1.f - sigmoidf_(acc[nt][2] + bb.x), 1.f - sigmoidf_(acc[nt][3] + bb.y));
-                }
-                w = acquire_block(b++);                               /* n gate: h = (1 - z) * tanh(n + b_in + r * b_hn) */
-                gemm_block<kHid / 16>(acc, a, w, (kHid + kPadK) * 2);
+                    for (int k = 0; k < 6; ++k) l[k] = q ? l1[k] : l0[k];
+                    if (out_logits) {
 #pragma unroll
-                for (int nt = 0; nt < 16; ++nt) {
-                    const float2 bb = bias2(op.b_ofs, 2, nt);
-                    const float2 r0 = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162 *>(&rb[nt][0]));
-                    const float2 r1 = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162 *>(&rb[nt][1]));
-                    const float2 z0 = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162 *>(&omz[nt][0]));
-                    const float2 z1 = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162 *>(&omz[nt][1]));
-                    acc[nt][0] = z0.x * tanhf_(acc[nt][0] + bb.x + r0.x); acc[nt][1] = z0.y * tanhf_(acc[nt][1] + bb.y + r0.y);
-                    acc[nt][2] = z1.x * tanhf_(acc[nt][2] + bb.x + r1.x); acc[nt][3] = z1.y * tanhf_(acc[nt][3] + bb.y + r1.y);
-                }
-                repack(a, acc);
-            } else {                                                  /* HEAD: 8 output rows, one n-tile */
-                const uint32_t w = acquire_block(b++);
-                float lg[4] = {0.f, 0.f, 0.f, 0.f};
-                const uint32_t lane_addr = w + (uint32_t)(lane & 7) * ((kHid + kPadK) * 2) + (uint32_t)(lane >> 3) * 16u;
+                        for (int k = 0; k < 6; ++k) out_logits[lr * 6 + k] = l[k];
+                    }
+                    if (do_sample) {
+                        float m = l[0];
 #pragma unroll
-                for (int kp = 0; kp < kHid / 32; ++kp) {              /* two k-steps per ldmatrix.x4 */
-                    uint32_t bf[4];
-                    ldmatrix_x4(bf, lane_addr + (uint32_t)kp * 64u);
-                    mma_bf16(lg, a[2 * kp], bf[0], bf[1]);
-                    mma_bf16(lg, a[2 * kp + 1], bf[2], bf[3]);
-                }
-                const float2 bb = __ldg(reinterpret_cast<const float2 *>(blob + op.b_ofs) + q);
-                lg[0] += bb.x; lg[1] += bb.y; lg[2] += bb.x; lg[3] += bb.y;
-                /* the 8 logits of a row sit in the 4 lanes of a quad: lane q = 0 takes row g, lane q = 1 row g + 8 */
-                float l0[8], l1[8];
+                        for (int k = 1; k < 6; ++k) m = fmaxf(m, l[k]);
+                        float wgt[6];
 #pragma unroll
-                for (int j = 0; j < 4; ++j) {
-                    const int src = (lane & ~3) + j;
-                    l0[2 * j] = __shfl_sync(0xffffffffu, lg[0], src); l0[2 * j + 1] = __shfl_sync(0xffffffffu, lg[1], src);
-                    l1[2 * j] = __shfl_sync(0xffffffffu, lg[2], src); l1[2 * j + 1] = __shfl_sync(0xffffffffu, lg[3], src);
-                }
-                if (q < 2) {
-                    const size_t lr = (size_t)tile * kTileRows + warp * 16 + g + (q ? 8 : 0);
-                    if (lr < rows) {
-                        float l[6];
-#pragma unroll
-                        for (int k = 0; k < 6; ++k) l[k] = q ? l1[k] : l0[k];
-                        if (out_logits) {
-#pragma unroll
-                            for (int k = 0; k < 6; ++k) out_logits[lr * 6 + k] = l[k];
-                        }
-                        if (do_sample) {
-                            float m = l[0];
-#pragma unroll
-                            for (int k = 1; k < 6; ++k) m = fmaxf(m, l[k]);
-                            float wgt[6];
-#pragma unroll
-                            for (int k = 0; k < 6; ++k) wgt[k] = __expf(l[k] - m);
-                            const int pick = sample_and_write(wgt, draw_key, row_begin + (uint32_t)lr, action);
-                            if (out_index) out_index[lr] = pick;
-                        }
+                        for (int k = 0; k < 6; ++k) wgt[k] = __expf(l[k] - m);
+                        const int pick = sample_and_write(wgt, draw_key, row_begin + (uint32_t)lr, action);
+                        if (out_index) out_index[lr] = pick;
                     }
                 }
             }
@@ -344,6 +360,8 @@ const char *policy_plan(const mbots_policy_program &p, uint64_t blob_bytes, Fuse
         for (uint32_t j = 0; j < blocks; ++j) {
             plan.ofs[plan.n_blocks] = op.w_ofs + j * bytes;
             plan.bytes[plan.n_blocks] = bytes;
+            plan.op_of[plan.n_blocks] = (uint8_t)i;
+            plan.gate_of[plan.n_blocks] = (uint8_t)j;
             ++plan.n_blocks;
         }
     }
