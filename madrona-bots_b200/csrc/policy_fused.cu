@@ -27,7 +27,8 @@ constexpr int kWBufBytes = kHid * (kHid + kPadK) * 2;      /* largest weight blo
 constexpr int kObsBytes = kTileRows * (kObsK + kPadK) * 2; /* 22,528 B */
 constexpr int kFusedThreads = 256;
 
-size_t policy_fused_smem_bytes() { return 2 * (size_t)kWBufBytes + kObsBytes; }
+constexpr int kWBufs = 3;                /* weight blocks in flight: the one in use + two being fetched */
+size_t policy_fused_smem_bytes() { return kWBufs * (size_t)kWBufBytes + kObsBytes; }
 
 /* ---- tensor-core and async-copy primitives ---- */
 __device__ __forceinline__ void mma_bf16(float (&c)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1)
@@ -49,6 +50,7 @@ __device__ __forceinline__ void cp_async16(uint32_t smem_addr, const void *gptr)
 }
 __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;"); }
 __device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_group 0;" ::: "memory"); }
+__device__ __forceinline__ void cp_async_wait_but_one() { asm volatile("cp.async.wait_group 1;" ::: "memory"); }
 
 __device__ __forceinline__ uint32_t pack_bf16(float lo, float hi)
 {
@@ -138,25 +140,26 @@ policy_fused_kernel(ObsPtrs o, int32_t *__restrict__ action, uint32_t row_begin,
 {
     extern __shared__ __align__(128) unsigned char smem[];
     const uint32_t smem_base = (uint32_t)__cvta_generic_to_shared(smem);
-    const uint32_t obs_base = smem_base + 2u * kWBufBytes;
-    __nv_bfloat16 *obs_tile = reinterpret_cast<__nv_bfloat16 *>(smem + 2 * kWBufBytes);
+    const uint32_t obs_base = smem_base + (uint32_t)kWBufs * kWBufBytes;
+    __nv_bfloat16 *obs_tile = reinterpret_cast<__nv_bfloat16 *>(smem + kWBufs * kWBufBytes);
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, g = lane >> 2, q = lane & 3;
     const Key draw_key = key_split(key_init(seed), draw);
 
-    auto issue_block = [&](int b) {       /* all threads: 16-byte chunks of block b into buffer b & 1 */
+    auto issue_block = [&](int b) {       /* all threads: 16-byte chunks of block b into buffer b % kWBufs */
         if (b < plan.n_blocks) {
             const unsigned char *src = blob + plan.ofs[b];
-            const uint32_t dst = smem_base + (uint32_t)(b & 1) * kWBufBytes;
+            const uint32_t dst = smem_base + (uint32_t)(b % kWBufs) * kWBufBytes;
             for (uint32_t c = (uint32_t)tid * 16u; c < plan.bytes[b]; c += kFusedThreads * 16u) cp_async16(dst + c, src + c);
         }
         cp_async_commit();
     };
-    /* block b has landed and every warp is done with block b - 1: start fetching block b + 1 */
+    /* block b has landed (only the group of block b + 1 may still be in flight) and every warp is done with block
+     * b - 1, whose buffer the fetch of block b + 2 now reuses */
     auto acquire_block = [&](int b) -> uint32_t {
-        cp_async_wait_all();
+        cp_async_wait_but_one();
         __syncthreads();
-        issue_block(b + 1);
-        return smem_base + (uint32_t)(b & 1) * kWBufBytes;
+        issue_block(b + 2);
+        return smem_base + (uint32_t)(b % kWBufs) * kWBufBytes;
     };
     auto bias2 = [&](uint32_t b_ofs, int vec, int nt) -> float2 {
         return __ldg(reinterpret_cast<const float2 *>(blob + b_ofs + (size_t)vec * (kHid * 4)) + nt * 4 + q);
@@ -165,6 +168,7 @@ policy_fused_kernel(ObsPtrs o, int32_t *__restrict__ action, uint32_t row_begin,
     for (uint32_t tile = blockIdx.x; (size_t)tile * kTileRows < rows; tile += gridDim.x) {
         __syncthreads();                  /* the previous tile no longer reads shared memory */
         issue_block(0);
+        issue_block(1);
         /* construct_obs of this tile's rows, bf16, zero padded to 80 columns / 128 rows: two threads per row, each
          * converts 16 depth and 16 semantic bytes (one 16-byte load each); the even one adds the five floats.
          * Every load of a thread is issued before the first conversion: one DRAM round trip per tile. */
