@@ -48,6 +48,8 @@ MOVED_BYTES_EXPORT = 280 + 280 + 36 + 64 + 4 + 2 + 41
 # dram__bytes_read.sum + dram__bytes_write.sum of export_kernel<FAST> per agent, from the committed
 # `ncu --set full` capture (profiles/r1d_ncu_full_summary.txt: 705.4 MB + 809.1 MB at 2,173,116 agents)
 NCU_TRAFFIC_BYTES_PER_AGENT_EXPORT = (705.409024e6 + 809.079040e6) / 2173116.0
+# same capture (profiles/r1e_ncu_full_summary.txt): what actually bounds the kernel is instruction issue
+NCU_EXPORT_ISSUE = {"warp_instructions_per_world": 461542924 / 65536.0, "issue_active_frac": 0.712}
 
 
 def measured_peaks():
@@ -357,7 +359,10 @@ def run_ours(args, rank, world, local_rank):
                      "algo_bytes_per_agent": ALGO_BYTES["export_sense"],
                      "moved_bytes_per_agent": MOVED_BYTES_EXPORT,
                      "achieved_moved": MOVED_BYTES_EXPORT * agents_per_launch / (k_ms * 1e-3) / 1e9 if k_ms > 0 else 0.0,
-                     "agents_per_launch": agents_per_launch, "kernel_ms": k_ms},
+                     "agents_per_launch": agents_per_launch, "kernel_ms": k_ms,
+                     "note": "issue-bound, not HBM-bound (32-ray sensor arithmetic): see issue_*",
+                     "issue_active_frac_ncu": NCU_EXPORT_ISSUE["issue_active_frac"],
+                     "issue_warp_instructions_per_world_ncu": NCU_EXPORT_ISSUE["warp_instructions_per_world"]},
         "kernels": kernels,
         "episode_stats": dict(zip(("agent_steps", "steps", "births", "deaths", "respawns", "overflow"),
                                   (tot[0], tot[1], tot[10], tot[11], tot[12], tot[13]))),
