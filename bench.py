@@ -329,7 +329,7 @@ def run_ours(args, rank, world, local_rank):
     e2e_value = tot_e[0] / (ms_e * 1e-3)
 
     if rank != 0:
-        return
+        return None
     peak, peak_src = measured_peaks()
     agents_per_launch = local_agent_steps / max(1, args.steps)
     k_ms = prof["export_sense"]["ms"]
@@ -369,7 +369,7 @@ def run_ours(args, rank, world, local_rank):
     }
     if world == 1 and not args.no_cpu_baseline:
         line["cpu_baseline"] = cpu_baseline_sample()
-    print(json.dumps(line), flush=True)
+    return line
 
 
 def main():
@@ -393,19 +393,28 @@ def main():
     if args.impl == "reference":
         run_reference(args, rank, world)
         return
-    # stdout carries exactly one JSON line: NCCL's own banner / debug output goes to stderr
-    os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
+    # stdout carries exactly one JSON line: while the run lasts, file descriptor 1 points at stderr, so that
+    # banners written by native libraries (NCCL prints its version to stdout under NCCL_DEBUG) land there
+    sys.stdout.flush()
+    saved_stdout = os.dup(1)
+    os.dup2(2, 1)
+    line = None
     if world > 1:
         import torch
         import torch.distributed as dist
         torch.cuda.set_device(local_rank)
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
     try:
-        run_ours(args, rank, world, local_rank)
+        line = run_ours(args, rank, world, local_rank)
     finally:
         if world > 1:
             import torch.distributed as dist
             dist.destroy_process_group()
+        sys.stdout.flush()
+        os.dup2(saved_stdout, 1)
+        os.close(saved_stdout)
+    if line is not None:
+        print(json.dumps(line), flush=True)
 
 
 if __name__ == "__main__":
