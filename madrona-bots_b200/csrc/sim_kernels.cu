@@ -971,14 +971,15 @@ __global__ void __launch_bounds__(256) shift_kernel(SimDev d, int cur)
 /* ------------------------------------------------------------------------- */
 /* episode statistics and debug gathers (not on the hot path)                  */
 
-__global__ void stats_reduce_kernel(SimDev d, long long *out)
+/* out[16] must be zero on entry; every CTA adds its share */
+__global__ void __launch_bounds__(256) stats_reduce_kernel(SimDev d, long long *out)
 {
-    __shared__ long long acc[16];
-    if (threadIdx.x < 16) acc[threadIdx.x] = 0;
+    __shared__ long long acc[14];
+    if (threadIdx.x < 14) acc[threadIdx.x] = 0;
     __syncthreads();
     long long l[14];
     for (int k = 0; k < 14; ++k) l[k] = 0;
-    for (uint32_t w = threadIdx.x; w < d.numWorlds; w += blockDim.x) {
+    for (uint32_t w = blockIdx.x * blockDim.x + threadIdx.x; w < d.numWorlds; w += gridDim.x * blockDim.x) {
         const int4 c = d.speciesCount[w], h = d.speciesHealth[w];
         const WorldStats ws = d.wstats[w];
         l[0] += c.x; l[1] += c.y; l[2] += c.z; l[3] += c.w;
@@ -986,14 +987,18 @@ __global__ void stats_reduce_kernel(SimDev d, long long *out)
         l[8] += ws.births; l[9] += ws.deaths; l[10] += ws.respawns; l[11] += ws.overflow;
         l[12] += ws.eaten; l[13] += ws.shots;
     }
-    for (int k = 0; k < 14; ++k) atomicAdd(reinterpret_cast<unsigned long long *>(&acc[2 + k]), (unsigned long long)l[k]);
-    __syncthreads();
-    if (threadIdx.x == 0) {
-        acc[0] = (long long)d.totals->agentSteps;
-        acc[1] = (long long)d.totals->steps;
+    for (int k = 0; k < 14; ++k) {
+        long long v = l[k];
+        for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(FULL, v, o);
+        if ((threadIdx.x & 31) == 0 && v) atomicAdd(reinterpret_cast<unsigned long long *>(&acc[k]), (unsigned long long)v);
     }
     __syncthreads();
-    if (threadIdx.x < 16) out[threadIdx.x] = acc[threadIdx.x];
+    if (threadIdx.x < 14 && acc[threadIdx.x])
+        atomicAdd(reinterpret_cast<unsigned long long *>(&out[2 + threadIdx.x]), (unsigned long long)acc[threadIdx.x]);
+    if (blockIdx.x == 0 && threadIdx.x == 0) {
+        out[0] = (long long)d.totals->agentSteps;
+        out[1] = (long long)d.totals->steps;
+    }
 }
 
 /* what: 0 pose (A,4) float, 1 health, 2 species, 3 target (A,1) int32; agent order */
@@ -1078,7 +1083,10 @@ void launch_shift(const SimDev &d, int cur, uint32_t rows_upper, cudaStream_t s)
 
 void launch_stats_reduce(const SimDev &d, long long *out16, cudaStream_t s)
 {
-    stats_reduce_kernel<<<1, 1024, 0, s>>>(d, out16);
+    cudaMemsetAsync(out16, 0, 16 * sizeof(long long), s);
+    unsigned blocks = (d.numWorlds + 255) / 256;
+    if (blocks > 148u * 4u) blocks = 148u * 4u;
+    stats_reduce_kernel<<<blocks, 256, 0, s>>>(d, out16);
 }
 
 void launch_debug_gather(const SimDev &d, int what, void *out, cudaStream_t s)
