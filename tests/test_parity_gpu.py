@@ -226,3 +226,38 @@ def test_full_size_properties(cuda_device):
     assert torch.equal(st_p[:, 1], st_c[:, 0]) and torch.equal(st_p[:, 2:], st_c[:, 2:])
     sim.shift_observations()
     assert torch.equal(sim.position_tensor(True).to_torch(), p1)
+
+
+def test_reference_plumbing_single_world_1000_steps(cuda_device):
+    """BASELINE.json configs[0]: the loop of learn/env.py:46-98 / learn/training_loop.py:36-137 against one world
+    for 1,000 steps -- step(), species slices from species_count_tensor().sum(0).cumsum(0), construct_obs of cur
+    and prev rows, one-hot actions written per species slice, shift_observations() once per species -- with the
+    oracle fed the same action tensor. Every export stays bit-identical."""
+    import torch
+    o, g = make_pair(1, 69, 32)
+    gen = torch.Generator(device="cuda").manual_seed(7)
+    for epoch in range(1, 1001):
+        o.step(); g.step()
+        counts = g.species_count_tensor().to_torch()
+        assert counts.shape == (1, 4) and counts.dtype == torch.int32
+        ends = counts.sum(dim=0).cumsum(dim=0, dtype=int)
+        starts = torch.cat((torch.zeros(1, dtype=torch.int, device="cuda"), ends[:-1]))
+        action = g.action_tensor(False).to_torch()
+        A = action.shape[0]
+        for sp in range(4):
+            a, b = int(starts[sp]), min(int(ends[sp]), A)       # counts are taken before the respawn (sim.cpp:804-836)
+            obs = torch.cat((g.depth_tensor(False).to_torch()[a:b, :], g.health_tensor(False).to_torch()[a:b, :],
+                             g.position_tensor(False).to_torch()[a:b, :], g.semantic_tensor(False).to_torch()[a:b, :],
+                             g.surrounding_tensor(False).to_torch()[a:b, :]), dim=1)
+            assert obs.shape == (b - a, 69)
+            picks = torch.randint(0, 6, (b - a,), generator=gen, device="cuda")
+            one_hot = torch.zeros(b - a, 6, device="cuda")
+            one_hot.scatter_(1, picks.unsqueeze(1), 1)
+            g.shift_observations()                              # inside the species loop, as the reference has it
+            action[a:b, :] = one_hot.int()
+            o.shift_observations()
+            o.tensor("ACTION")[a:b, :] = one_hot.int().cpu().numpy()
+        if epoch % 100 == 0 or epoch == 1:
+            compare(o, g, f"epoch {epoch}")
+    st = o.episode_stats()
+    assert st[1] == 1000 and st[11] > 0 and st[12] > 0
