@@ -2,10 +2,15 @@
  * networks of the reference (learn/models.py:14-93: feature MLP, one recurrent layer, actor head; checkpoint
  * format learn/ckpt.py:28-32) flattened into a short program over one device blob.
  *
- * Blob layout (built by madrona_bots/policy.py, all offsets multiples of 16 bytes):
- *   weight block  [rows][k_pad + 8] bfloat16, row = output feature, k = input feature, zero padded;
- *                 rows = 128 (HEAD: 8). The 8 trailing elements of a row are padding (shared-memory layout).
- *   bias vector   float32.
+ * Blob layout (built by madrona_bots/policy.py, all offsets multiples of 16 bytes), two weight-block formats:
+ *   MBOTS_LAYOUT_ROWPAD  weight block [rows][k_pad + 8] bfloat16, row = output feature, k = input feature, zero
+ *                 padded; rows = 128 (HEAD: 8). The 8 trailing elements of a row are padding (shared-memory
+ *                 layout of the mma.sync kernel, policy_fused.cu).
+ *   MBOTS_LAYOUT_SW128   every weight block is 32 KB: the canonical K-major SWIZZLE_128B shared-memory image of a
+ *                 [128 rows][128 k] bfloat16 operand that tcgen05.mma reads (policy_umma.cu): element (row, k) at
+ *                 byte (k/64)*16384 + (row/8)*1024 + (row%8)*128 + (((k%64)/8) ^ (row%8))*16 + (k%8)*2; unused
+ *                 rows / columns zero (HEAD: rows 0..5 used).
+ *   bias vector   float32 (both layouts).
  * Ops, applied in order to a tile of 128 agents whose first input is the (69 -> k_pad 80) observation row of
  * learn/util.py:23-29:
  *   LINEAR  x <- act(W x + b)                       1 block, 128 biases
@@ -24,6 +29,7 @@ enum mbots_policy_act {
     MBOTS_ACT_NONE = 0, MBOTS_ACT_TANH = 1, MBOTS_ACT_ELU = 2, MBOTS_ACT_LOGSIGMOID = 3,
     MBOTS_ACT_LEAKYRELU = 4, MBOTS_ACT_RELU = 5, MBOTS_ACT_SIGMOID = 6
 };
+enum mbots_policy_layout { MBOTS_LAYOUT_ROWPAD = 0, MBOTS_LAYOUT_SW128 = 1 };
 #define MBOTS_POLICY_MAX_OPS 12
 
 typedef struct mbots_policy_op {
@@ -36,6 +42,7 @@ typedef struct mbots_policy_op {
 
 typedef struct mbots_policy_program {
     int32_t n_ops;
+    int32_t layout;    /* mbots_policy_layout: which kernel the weight blocks were laid out for */
     mbots_policy_op ops[MBOTS_POLICY_MAX_OPS];
 } mbots_policy_program;
 

@@ -650,6 +650,9 @@ namespace mbk {
 const char *launch_policy_fused(const ObsSet &o, uint32_t row_begin, uint32_t rows, const void *blob, uint64_t blob_bytes,
                                 const mbots_policy_program &prog, uint32_t seed, uint32_t draw, int do_sample,
                                 float *out_logits, int32_t *out_index, cudaStream_t s);
+const char *launch_policy_umma(const ObsSet &o, uint32_t row_begin, uint32_t rows, const void *blob, uint64_t blob_bytes,
+                               const mbots_policy_program &prog, uint32_t seed, uint32_t draw, int do_sample,
+                               float *out_logits, int32_t *out_index, cudaStream_t s);
 }
 
 extern "C" int mbots_policy_act(mbots_sim *s, uint32_t row_begin, uint32_t row_end, const void *blob, uint64_t blob_bytes,
@@ -659,8 +662,10 @@ extern "C" int mbots_policy_act(mbots_sim *s, uint32_t row_begin, uint32_t row_e
     if (!s || !blob || !program) return fail(MBOTS_EINVAL, "null argument");
     if (row_begin > row_end || row_end > s->totalAgents) return fail(MBOTS_EINVAL, "row range outside [0, num_agents]");
     DeviceGuard g(s->device);
-    const char *err = launch_policy_fused(s->d.obs[s->cur], row_begin, row_end - row_begin, blob, blob_bytes, *program, seed,
-                                          draw, sample != 0, out_logits, out_index, (cudaStream_t)stream);
+    if (program->layout != MBOTS_LAYOUT_ROWPAD && program->layout != MBOTS_LAYOUT_SW128) return fail(MBOTS_EINVAL, "unknown blob layout");
+    const auto launch = program->layout == MBOTS_LAYOUT_SW128 ? launch_policy_umma : launch_policy_fused;
+    const char *err = launch(s->d.obs[s->cur], row_begin, row_end - row_begin, blob, blob_bytes, *program, seed, draw,
+                             sample != 0, out_logits, out_index, (cudaStream_t)stream);
     if (err) return fail(MBOTS_EINVAL, err);
     CU(cudaGetLastError());
     s->launches += row_end > row_begin ? 1 : 0;

@@ -1,0 +1,477 @@
+/* policy_umma.cu -- the acting path of learn/training_loop.py:52-83,136 on the 5th-generation tensor cores.
+ *
+ * Same contract as policy_fused.cu (one kernel per species: construct_obs -> species network -> softmax ->
+ * Threefry sample -> one-hot action row), different engine: every layer is a 128 x N x K `tcgen05.mma` issued by
+ * ONE thread, operands in shared memory in the canonical K-major SWIZZLE_128B layout, accumulator in tensor
+ * memory. A persistent CTA per SM keeps TWO tiles of 128 agents in flight: while the four epilogue warps of one
+ * tile pull its accumulator out of TMEM (tcgen05.ld: one thread = one agent row), apply bias / activation / gate
+ * arithmetic and write the next layer's A operand back to shared memory (bf16, swizzled), the tensor core is
+ * already multiplying the other tile. Weight blocks (bf16, pre-swizzled by the host, 32 KB each) arrive through a
+ * three-deep ring of 1-D bulk copies (cp.async.bulk -> mbarrier complete_tx) issued by the MMA thread.
+ *
+ *   warps 0-3   epilogue of tile 0        warps 4-7   epilogue of tile 1        warp 8   lane 0: copies + MMA issue
+ *   mbarriers   w_full[3] / w_empty[3]    weight ring
+ *               acc_full[2]               tcgen05.commit: accumulator of tile t is complete
+ *               a_ready[2]                epilogue of tile t drained TMEM and (re)wrote its A operand
+ * The descriptor recipe was validated in isolation first (tools/probes/umma_probe.cu).
+ */
+#include <cuda_runtime.h>
+#include <cuda_bf16.h>
+#include <stdint.h>
+#include "sim_dev.h"
+#include "policy_dev.cuh"
+#include "../../include/mbots_policy.h"
+
+namespace mbk {
+
+constexpr int kUTile = 128;                         /* agents per tile = UMMA M */
+constexpr int kUBlockBytes = 128 * 128 * 2;          /* one operand: [128 rows][128 k] bf16 = two 16 KB K-blocks */
+constexpr int kUThreads = 288;                      /* 8 epilogue warps + 1 issue warp */
+constexpr int kURing = 3;
+constexpr int kUTmemCols = 512;                     /* per tile: 128 accumulator columns + 128 scratch columns (x2 tiles, padded to 256 each) */
+
+/* shared memory: [weights x3][A operand x2] + barriers (1 KB aligned base) */
+constexpr int kUSmemBytes = (kURing + 2) * kUBlockBytes + 1024 /* alignment slack */ + 256 /* barriers */;
+size_t policy_umma_smem_bytes() { return kUSmemBytes; }
+
+/* byte offset of (row, k) in a K-major SWIZZLE_128B operand: K-blocks of 64, 8-row atoms of 1024 B, 16-byte
+ * chunks XOR-ed with the row inside the atom */
+__host__ __device__ __forceinline__ uint32_t sw128_chunk_offset(uint32_t row, uint32_t chunk /* k / 8 */)
+{
+    return (chunk >> 3) * 16384u + (row >> 3) * 1024u + (row & 7u) * 128u + (((chunk & 7u) ^ (row & 7u)) << 4);
+}
+
+__device__ __forceinline__ uint64_t umma_desc(uint32_t smem_addr)
+{
+    return (uint64_t)((smem_addr >> 4) & 0x3fffu) | ((uint64_t)1 << 16) /* LBO 16 B */ | ((uint64_t)64 << 32) /* SBO 1024 B */ |
+           ((uint64_t)1 << 46) /* version */ | ((uint64_t)2 << 61) /* SWIZZLE_128B */;
+}
+
+__device__ __forceinline__ uint32_t umma_idesc(uint32_t n)      /* bf16 x bf16 -> f32, M = 128, both K-major */
+{
+    return (1u << 4) | (1u << 7) | (1u << 10) | ((n >> 3) << 17) | ((128u >> 4) << 24);
+}
+
+__device__ __forceinline__ void umma_bf16(uint32_t tmem_d, uint64_t da, uint64_t db, uint32_t idesc, uint32_t accumulate)
+{
+    asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+                 "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
+                 ::"r"(tmem_d), "l"(da), "l"(db), "r"(idesc), "r"(accumulate) : "memory");
+}
+__device__ __forceinline__ void umma_commit(uint32_t bar)
+{
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void fence_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count)
+{
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint32_t bar)
+{
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes)
+{
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity)
+{
+    uint32_t done = 0;
+    while (!done)
+        asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}"
+                     : "=r"(done) : "r"(bar), "r"(parity) : "memory");
+}
+__device__ __forceinline__ void bulk_copy_g2s(uint32_t dst, const void *src, uint32_t bytes, uint32_t bar)
+{
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 ::"r"(dst), "l"(src), "r"(bytes), "r"(bar) : "memory");
+}
+
+/* 32 consecutive accumulator columns of this thread's row (TMEM lane) */
+__device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&v)[32])
+{
+    asm volatile("tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+                 "{%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,%16,%17,%18,%19,%20,%21,%22,%23,%24,%25,%26,%27,%28,%29,%30,%31}, [%32];"
+                 : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]),
+                   "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15]),
+                   "=r"(v[16]), "=r"(v[17]), "=r"(v[18]), "=r"(v[19]), "=r"(v[20]), "=r"(v[21]), "=r"(v[22]), "=r"(v[23]),
+                   "=r"(v[24]), "=r"(v[25]), "=r"(v[26]), "=r"(v[27]), "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31])
+                 : "r"(taddr) : "memory");
+    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+}
+
+__device__ __forceinline__ uint32_t upack_bf16(float lo, float hi)
+{
+    const __nv_bfloat162 v = __floats2bfloat162_rn(lo, hi);
+    return *reinterpret_cast<const uint32_t *>(&v);
+}
+__device__ __forceinline__ float2 uunpack_bf16(uint32_t u)
+{
+    return __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162 *>(&u));
+}
+
+__device__ __forceinline__ float utanh(float x)
+{
+    float y;
+    asm("tanh.approx.f32 %0, %1;" : "=f"(y) : "f"(x));
+    return y;
+}
+__device__ __forceinline__ float usigmoid(float x) { return fmaf(0.5f, utanh(0.5f * x), 0.5f); }
+
+template <int ACT>
+__device__ __forceinline__ float uact(float x)
+{
+    if (ACT == MBOTS_ACT_TANH) return utanh(x);
+    if (ACT == MBOTS_ACT_ELU) return x > 0.f ? x : __expf(x) - 1.f;
+    if (ACT == MBOTS_ACT_LOGSIGMOID) return fminf(x, 0.f) - __logf(1.f + __expf(-fabsf(x)));
+    if (ACT == MBOTS_ACT_LEAKYRELU) return x > 0.f ? x : 0.01f * x;
+    if (ACT == MBOTS_ACT_RELU) return fmaxf(x, 0.f);
+    if (ACT == MBOTS_ACT_SIGMOID) return usigmoid(x);
+    return x;
+}
+
+__device__ __forceinline__ void tmem_st32(uint32_t taddr, const uint32_t (&v)[32])
+{
+    asm volatile("tcgen05.st.sync.aligned.32x32b.x32.b32 [%0], "
+                 "{%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,%16,%17,%18,%19,%20,%21,%22,%23,%24,%25,%26,%27,%28,%29,%30,%31,%32};"
+                 ::"r"(taddr), "r"(v[0]), "r"(v[1]), "r"(v[2]), "r"(v[3]), "r"(v[4]), "r"(v[5]), "r"(v[6]), "r"(v[7]),
+                   "r"(v[8]), "r"(v[9]), "r"(v[10]), "r"(v[11]), "r"(v[12]), "r"(v[13]), "r"(v[14]), "r"(v[15]),
+                   "r"(v[16]), "r"(v[17]), "r"(v[18]), "r"(v[19]), "r"(v[20]), "r"(v[21]), "r"(v[22]), "r"(v[23]),
+                   "r"(v[24]), "r"(v[25]), "r"(v[26]), "r"(v[27]), "r"(v[28]), "r"(v[29]), "r"(v[30]), "r"(v[31])
+                 : "memory");
+    asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
+}
+
+/* 32 activations of this thread's row -> four 16-byte chunks of the A operand */
+__device__ __forceinline__ void store_a_chunk(unsigned char *a_tile, uint32_t row, int c, const float (&x)[32])
+{
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+        const uint4 p = make_uint4(upack_bf16(x[8 * j], x[8 * j + 1]), upack_bf16(x[8 * j + 2], x[8 * j + 3]),
+                                   upack_bf16(x[8 * j + 4], x[8 * j + 5]), upack_bf16(x[8 * j + 6], x[8 * j + 7]));
+        *reinterpret_cast<uint4 *>(a_tile + sw128_chunk_offset(row, (uint32_t)(c * 4 + j))) = p;
+    }
+}
+
+__device__ __forceinline__ void load_bias32(const float *bias, int c, float (&b)[32])
+{
+    const float4 *p = reinterpret_cast<const float4 *>(bias) + c * 8;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+        const float4 v = __ldg(p + j);
+        b[4 * j] = v.x; b[4 * j + 1] = v.y; b[4 * j + 2] = v.z; b[4 * j + 3] = v.w;
+    }
+}
+
+template <int ACT>
+__device__ __forceinline__ void epi_linear(uint32_t acc, const float *bias, unsigned char *a_tile, uint32_t row)
+{
+#pragma unroll 1
+    for (int c = 0; c < 4; ++c) {
+        uint32_t v[32];
+        float b[32], x[32];
+        tmem_ld32(acc + (uint32_t)c * 32u, v);
+        load_bias32(bias, c, b);
+#pragma unroll
+        for (int i = 0; i < 32; ++i) x[i] = uact<ACT>(__uint_as_float(v[i]) + b[i]);
+        store_a_chunk(a_tile, row, c, x);
+    }
+}
+
+struct UmmaPlan {                          /* weight blocks (32 KB each) in streaming order */
+    int32_t n_blocks;
+    uint32_t ofs[3 * MBOTS_POLICY_MAX_OPS];
+    uint8_t op_of[3 * MBOTS_POLICY_MAX_OPS];
+    uint8_t gate_of[3 * MBOTS_POLICY_MAX_OPS];
+};
+
+struct UObsPtrs { const uint8_t *depth; const float *health; const float *position; const int8_t *semantic; const float *surrounding; };
+
+__global__ void __launch_bounds__(kUThreads, 1)
+policy_umma_kernel(UObsPtrs o, int32_t *__restrict__ action, uint32_t row_begin, uint32_t rows, const unsigned char *__restrict__ blob,
+                   mbots_policy_program prog, UmmaPlan plan, uint32_t seed, uint32_t draw, int do_sample,
+                   float *__restrict__ out_logits, int32_t *__restrict__ out_index)
+{
+    extern __shared__ unsigned char smem_raw[];
+    unsigned char *smem = reinterpret_cast<unsigned char *>((reinterpret_cast<uintptr_t>(smem_raw) + 1023u) & ~(uintptr_t)1023u);
+    const uint32_t smem_base = (uint32_t)__cvta_generic_to_shared(smem);
+    const uint32_t w_base = smem_base, a_base = smem_base + kURing * kUBlockBytes, bar_base = a_base + 2 * kUBlockBytes;
+    unsigned char *a_ptr = smem + kURing * kUBlockBytes;
+    uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(smem + (kURing + 2) * kUBlockBytes + 128);
+    /* barriers: 8 bytes each */
+    auto W_FULL = [&](int i) { return bar_base + (uint32_t)i * 8u; };
+    auto W_EMPTY = [&](int i) { return bar_base + 24u + (uint32_t)i * 8u; };
+    auto ACC_FULL = [&](int t) { return bar_base + 48u + (uint32_t)t * 8u; };
+    auto A_READY = [&](int t) { return bar_base + 64u + (uint32_t)t * 8u; };
+
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    if (tid == 0) {
+        for (int i = 0; i < kURing; ++i) { mbar_init(W_FULL(i), 1); mbar_init(W_EMPTY(i), 1); }
+        for (int t = 0; t < 2; ++t) { mbar_init(ACC_FULL(t), 1); mbar_init(A_READY(t), 4); }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (warp == 8) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;"
+                     ::"r"((uint32_t)__cvta_generic_to_shared(tmem_slot)), "r"((uint32_t)kUTmemCols) : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem = *tmem_slot;
+    /* TMEM columns: tile t accumulator at t * 256, its scratch (LSTM cell / GRU helpers) at t * 256 + 128 */
+
+    const uint32_t n_tiles = (rows + kUTile - 1) / kUTile;
+    const uint32_t n_pairs = (n_tiles + 1) / 2;
+    const uint32_t my_pairs = blockIdx.x < n_pairs ? (n_pairs - blockIdx.x + gridDim.x - 1) / gridDim.x : 0;
+    const int B = plan.n_blocks;
+
+    if (warp < 8) {
+        /* ---------------- epilogue warps: thread = one agent row of tile t ---------------- */
+        const int t = warp >> 2, w4 = warp & 3;
+        const uint32_t r = (uint32_t)(w4 * 32 + lane);
+        unsigned char *a_tile = a_ptr + (size_t)t * kUBlockBytes;
+        const uint32_t acc = tmem + ((uint32_t)(w4 * 32) << 16) + (uint32_t)t * 256u, scratch = acc + 128u;
+        const Key draw_key = key_split(key_init(seed), draw);
+        uint32_t acc_phase = 0;
+        for (uint32_t it = 0; it < my_pairs; ++it) {
+            const uint32_t tile = (blockIdx.x + it * gridDim.x) * 2u + (uint32_t)t;
+            const size_t lr = (size_t)tile * kUTile + r;
+            const bool live = lr < rows;
+            /* construct_obs of this row -> A operand (80 columns = 10 chunks; the MMA reads 5 k-steps) */
+            {
+                const size_t row = (size_t)row_begin + (live ? lr : 0);
+                float x[80];
+#pragma unroll
+                for (int i = 0; i < 80; ++i) x[i] = 0.f;
+                if (live) {
+                    const uint4 d0 = __ldg(reinterpret_cast<const uint4 *>(o.depth + row * 32)), d1 = __ldg(reinterpret_cast<const uint4 *>(o.depth + row * 32) + 1);
+                    const uint4 s0 = __ldg(reinterpret_cast<const uint4 *>(o.semantic + row * 32)), s1 = __ldg(reinterpret_cast<const uint4 *>(o.semantic + row * 32) + 1);
+                    const float hl = __ldg(o.health + row);
+                    const float2 ps = __ldg(reinterpret_cast<const float2 *>(o.position) + row);
+                    const float2 su = __ldg(reinterpret_cast<const float2 *>(o.surrounding) + row);
+                    const uint32_t dw[8] = {d0.x, d0.y, d0.z, d0.w, d1.x, d1.y, d1.z, d1.w};
+                    const uint32_t sw[8] = {s0.x, s0.y, s0.z, s0.w, s1.x, s1.y, s1.z, s1.w};
+#pragma unroll
+                    for (int i = 0; i < 32; ++i) {
+                        x[i] = (float)((dw[i >> 2] >> (8 * (i & 3))) & 0xffu);
+                        x[35 + i] = (float)(int8_t)((sw[i >> 2] >> (8 * (i & 3))) & 0xffu);
+                    }
+                    x[32] = hl; x[33] = ps.x; x[34] = ps.y; x[67] = su.x; x[68] = su.y;
+                }
+#pragma unroll
+                for (int j = 0; j < 10; ++j) {
+                    const uint4 p = make_uint4(upack_bf16(x[8 * j], x[8 * j + 1]), upack_bf16(x[8 * j + 2], x[8 * j + 3]),
+                                               upack_bf16(x[8 * j + 4], x[8 * j + 5]), upack_bf16(x[8 * j + 6], x[8 * j + 7]));
+                    *reinterpret_cast<uint4 *>(a_tile + sw128_chunk_offset(r, (uint32_t)j)) = p;
+                }
+            }
+            fence_async_smem();
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(A_READY(t));
+
+            for (int b = 0; b < B; ++b) {
+                const mbots_policy_op op = prog.ops[plan.op_of[b]];
+                const int gate = plan.gate_of[b];
+                const float *bias = reinterpret_cast<const float *>(blob + op.b_ofs);
+                mbar_wait(ACC_FULL(t), acc_phase);
+                acc_phase ^= 1u;
+                tc_fence_after();
+                if (op.op == MBOTS_OP_LINEAR) {
+                    switch (op.act) {
+                    case MBOTS_ACT_TANH: epi_linear<MBOTS_ACT_TANH>(acc, bias, a_tile, r); break;
+                    case MBOTS_ACT_ELU: epi_linear<MBOTS_ACT_ELU>(acc, bias, a_tile, r); break;
+                    case MBOTS_ACT_LOGSIGMOID: epi_linear<MBOTS_ACT_LOGSIGMOID>(acc, bias, a_tile, r); break;
+                    case MBOTS_ACT_LEAKYRELU: epi_linear<MBOTS_ACT_LEAKYRELU>(acc, bias, a_tile, r); break;
+                    case MBOTS_ACT_RELU: epi_linear<MBOTS_ACT_RELU>(acc, bias, a_tile, r); break;
+                    case MBOTS_ACT_SIGMOID: epi_linear<MBOTS_ACT_SIGMOID>(acc, bias, a_tile, r); break;
+                    default: epi_linear<MBOTS_ACT_NONE>(acc, bias, a_tile, r); break;
+                    }
+                } else if (op.op == MBOTS_OP_LSTM0) {
+#pragma unroll 1
+                    for (int c = 0; c < 4; ++c) {
+                        uint32_t v[32], s[32];
+                        float bb[32];
+                        tmem_ld32(acc + (uint32_t)c * 32u, v);
+                        load_bias32(bias + gate * 128, c, bb);
+                        if (gate == 0) {                              /* i gate: park sigmoid(i) */
+#pragma unroll
+                            for (int i = 0; i < 32; ++i) s[i] = __float_as_uint(usigmoid(__uint_as_float(v[i]) + bb[i]));
+                            tmem_st32(scratch + (uint32_t)c * 32u, s);
+                        } else if (gate == 1) {                       /* g gate: c = sigmoid(i) * tanh(g) */
+                            tmem_ld32(scratch + (uint32_t)c * 32u, s);
+#pragma unroll
+                            for (int i = 0; i < 32; ++i) s[i] = __float_as_uint(__uint_as_float(s[i]) * utanh(__uint_as_float(v[i]) + bb[i]));
+                            tmem_st32(scratch + (uint32_t)c * 32u, s);
+                        } else {                                      /* o gate: h = sigmoid(o) * tanh(c) */
+                            float x[32];
+                            tmem_ld32(scratch + (uint32_t)c * 32u, s);
+#pragma unroll
+                            for (int i = 0; i < 32; ++i) x[i] = usigmoid(__uint_as_float(v[i]) + bb[i]) * utanh(__uint_as_float(s[i]));
+                            store_a_chunk(a_tile, r, c, x);
+                        }
+                    }
+                } else if (op.op == MBOTS_OP_GRU0) {                  /* biases: b_r, b_z, b_in, b_hn */
+#pragma unroll 1
+                    for (int c = 0; c < 4; ++c) {
+                        uint32_t v[32], s[32];
+                        float bb[32];
+                        tmem_ld32(acc + (uint32_t)c * 32u, v);
+                        load_bias32(bias + gate * 128, c, bb);
+                        if (gate == 0) {                              /* r gate: park r * b_hn (low bf16 half) */
+                            float hn[32];
+                            load_bias32(bias + 3 * 128, c, hn);
+#pragma unroll
+                            for (int i = 0; i < 32; ++i) s[i] = upack_bf16(usigmoid(__uint_as_float(v[i]) + bb[i]) * hn[i], 0.f);
+                            tmem_st32(scratch + (uint32_t)c * 32u, s);
+                        } else if (gate == 1) {                       /* z gate: add 1 - z (high bf16 half) */
+                            tmem_ld32(scratch + (uint32_t)c * 32u, s);
+#pragma unroll
+                            for (int i = 0; i < 32; ++i) s[i] = upack_bf16(uunpack_bf16(s[i]).x, 1.f - usigmoid(__uint_as_float(v[i]) + bb[i]));
+                            tmem_st32(scratch + (uint32_t)c * 32u, s);
+                        } else {                                      /* n gate: h = (1 - z) * tanh(n + b_in + r * b_hn) */
+                            float x[32];
+                            tmem_ld32(scratch + (uint32_t)c * 32u, s);
+#pragma unroll
+                            for (int i = 0; i < 32; ++i) {
+                                const float2 rz = uunpack_bf16(s[i]);
+                                x[i] = rz.y * utanh(__uint_as_float(v[i]) + bb[i] + rz.x);
+                            }
+                            store_a_chunk(a_tile, r, c, x);
+                        }
+                    }
+                } else {                                              /* HEAD: 6 logits in columns 0..5 */
+                    uint32_t v[32];
+                    tmem_ld32(acc, v);
+                    if (live) {
+                        float l[6];
+#pragma unroll
+                        for (int k = 0; k < 6; ++k) l[k] = __uint_as_float(v[k]) + __ldg(bias + k);
+                        if (out_logits) {
+#pragma unroll
+                            for (int k = 0; k < 6; ++k) out_logits[lr * 6 + k] = l[k];
+                        }
+                        if (do_sample) {
+                            float m = l[0];
+#pragma unroll
+                            for (int k = 1; k < 6; ++k) m = fmaxf(m, l[k]);
+                            float wgt[6];
+#pragma unroll
+                            for (int k = 0; k < 6; ++k) wgt[k] = __expf(l[k] - m);
+                            const int pick = sample_and_write(wgt, draw_key, row_begin + (uint32_t)lr, action);
+                            if (out_index) out_index[lr] = pick;
+                        }
+                    }
+                }
+                if (b + 1 < B) {          /* accumulator drained, A operand (re)written: the next block may be issued */
+                    fence_async_smem();
+                    tc_fence_before();
+                    __syncwarp();
+                    if (lane == 0) mbar_arrive(A_READY(t));
+                }
+            }
+        }
+    } else {
+        if (lane == 0) {
+        /* ---------------- issue thread: weight ring + tcgen05.mma ---------------- */
+        const uint32_t total = my_pairs * (uint32_t)B;
+        auto fetch = [&](uint32_t g) {     /* global block number g -> ring slot g % 3 */
+            if (g < total) {
+                const uint32_t slot = g % kURing;
+                mbar_expect_tx(W_FULL(slot), kUBlockBytes);
+                bulk_copy_g2s(w_base + slot * kUBlockBytes, blob + plan.ofs[g % (uint32_t)B], kUBlockBytes, W_FULL(slot));
+            }
+        };
+        for (uint32_t g = 0; g < (uint32_t)kURing; ++g) fetch(g);
+        uint32_t a_phase[2] = {0u, 0u};
+        uint32_t g = 0;
+        for (uint32_t it = 0; it < my_pairs; ++it) {
+            for (int b = 0; b < B; ++b, ++g) {
+                const uint32_t slot = g % kURing;
+                const mbots_policy_op op = prog.ops[plan.op_of[b]];
+                const uint32_t ksteps = op.k_pad >> 4;
+                const uint32_t idesc = umma_idesc(op.op == MBOTS_OP_HEAD ? 16u : 128u);
+                mbar_wait(W_FULL(slot), (g / kURing) & 1u);
+                for (int t = 0; t < 2; ++t) {
+                    mbar_wait(A_READY(t), a_phase[t]);
+                    a_phase[t] ^= 1u;
+                    tc_fence_after();
+                    const uint32_t a0 = a_base + (uint32_t)t * kUBlockBytes, b0 = w_base + slot * kUBlockBytes;
+                    for (uint32_t ks = 0; ks < ksteps; ++ks) {
+                        const uint32_t off = (ks >> 2) * 16384u + (ks & 3u) * 32u;
+                        umma_bf16(tmem + (uint32_t)t * 256u, umma_desc(a0 + off), umma_desc(b0 + off), idesc, ks > 0 ? 1u : 0u);
+                    }
+                    umma_commit(ACC_FULL(t));
+                }
+                umma_commit(W_EMPTY(slot));
+                if (g >= 1) {              /* the slot of block g - 1 is free once its products are done: refill it */
+                    mbar_wait(W_EMPTY((g - 1) % kURing), ((g - 1) / kURing) & 1u);
+                    fetch(g + 2);
+                }
+            }
+        }
+        }
+        __syncwarp();
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 8) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"((uint32_t)kUTmemCols) : "memory");
+}
+
+/* Host: validate a SW128-layout program against the blob and derive the streaming plan. Returns 0 or a message. */
+static const char *policy_umma_plan(const mbots_policy_program &p, uint64_t blob_bytes, UmmaPlan &plan)
+{
+    if (p.n_ops < 2 || p.n_ops > MBOTS_POLICY_MAX_OPS) return "program must hold 2..12 ops";
+    plan.n_blocks = 0;
+    for (int i = 0; i < p.n_ops; ++i) {
+        const mbots_policy_op &op = p.ops[i];
+        const bool first = i == 0, last = i == p.n_ops - 1;
+        if (first && (op.op != MBOTS_OP_LINEAR || op.k_pad != 80u)) return "the first op must be LINEAR with k_pad 80";
+        if (!first && op.k_pad != 128u) return "every op after the first takes 128 inputs";
+        if (last != (op.op == MBOTS_OP_HEAD)) return "HEAD must be the last op and only the last";
+        if (op.op < MBOTS_OP_LINEAR || op.op > MBOTS_OP_HEAD) return "unknown op";
+        if (op.act < MBOTS_ACT_NONE || op.act > MBOTS_ACT_SIGMOID) return "unknown activation";
+        if ((op.w_ofs | op.b_ofs) & 15u) return "offsets must be multiples of 16";
+        const uint32_t blocks = (op.op == MBOTS_OP_LSTM0 || op.op == MBOTS_OP_GRU0) ? 3u : 1u;
+        const uint32_t nbias = op.op == MBOTS_OP_HEAD ? 8u : op.op == MBOTS_OP_GRU0 ? 4u * 128u : blocks * 128u;
+        if ((uint64_t)op.w_ofs + (uint64_t)blocks * kUBlockBytes > blob_bytes || (uint64_t)op.b_ofs + 4ull * nbias > blob_bytes)
+            return "op reaches beyond the blob";
+        for (uint32_t j = 0; j < blocks; ++j) {
+            plan.ofs[plan.n_blocks] = op.w_ofs + j * (uint32_t)kUBlockBytes;
+            plan.op_of[plan.n_blocks] = (uint8_t)i;
+            plan.gate_of[plan.n_blocks] = (uint8_t)j;
+            ++plan.n_blocks;
+        }
+    }
+    return nullptr;
+}
+
+const char *launch_policy_umma(const ObsSet &o, uint32_t row_begin, uint32_t rows, const void *blob, uint64_t blob_bytes,
+                               const mbots_policy_program &prog, uint32_t seed, uint32_t draw, int do_sample,
+                               float *out_logits, int32_t *out_index, cudaStream_t s)
+{
+    UmmaPlan plan;
+    const char *err = policy_umma_plan(prog, blob_bytes, plan);
+    if (err || rows == 0) return err;
+    if (reinterpret_cast<uintptr_t>(blob) & 15u) return "the blob must be 16-byte aligned";
+    static bool attr_set = false;
+    if (!attr_set) {
+        cudaFuncSetAttribute(policy_umma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kUSmemBytes);
+        attr_set = true;
+    }
+    const uint32_t pairs = ((rows + kUTile - 1) / kUTile + 1) / 2;
+    int dev = 0, sms = 148;
+    if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    const uint32_t grid = pairs < (uint32_t)sms ? pairs : (uint32_t)sms;      /* persistent: one CTA per SM */
+    const UObsPtrs ptrs = {o.depth, o.health, o.position, o.semantic, o.surrounding};
+    policy_umma_kernel<<<grid, kUThreads, kUSmemBytes, s>>>(ptrs, o.action, row_begin, rows, static_cast<const unsigned char *>(blob),
+                                                            prog, plan, seed, draw, do_sample, out_logits, out_index);
+    return nullptr;
+}
+
+} // namespace mbk

@@ -35,10 +35,11 @@ class PolicyOp(ctypes.Structure):          # mbots_policy_op (include/mbots_poli
 
 
 class PolicyProgram(ctypes.Structure):     # mbots_policy_program
-    _fields_ = [("n_ops", ctypes.c_int32), ("ops", PolicyOp * 12)]
+    _fields_ = [("n_ops", ctypes.c_int32), ("layout", ctypes.c_int32), ("ops", PolicyOp * 12)]
 
 
 OP_LINEAR, OP_LSTM0, OP_GRU0, OP_HEAD = 0, 1, 2, 3
+LAYOUT_ROWPAD, LAYOUT_SW128 = 0, 1
 ACT = dict(NONE=0, Tanh=1, ELU=2, LogSigmoid=3, LeakyReLU=4, ReLU=5, Sigmoid=6)
 
 

@@ -159,11 +159,16 @@ class FusedPolicy:
     Restrictions of the kernel: hidden width 128, observation width 69, 6 actions (the reference's defaults,
     learn/training_loop.py:228-232) and the actor head Linear-ReLU-Linear of learn/models.py:33-37."""
 
-    def __init__(self, policy):
+    def __init__(self, policy, layout="sw128"):
+        """layout="sw128": 32 KB pre-swizzled weight blocks for the tcgen05 kernel (policy_umma.cu, the default);
+        layout="rowpad": padded rows for the mma.sync kernel (policy_fused.cu)."""
         import numpy as np
         import torch
         from . import _native
         H, PAD = 128, 8
+        if layout not in ("sw128", "rowpad"):
+            raise ValueError("layout must be 'sw128' or 'rowpad'")
+        self.layout = layout
         if policy.hidden_dim != H:
             raise ValueError("the fused kernel is built for hidden_dim 128")
         chunks, size = [], 0
@@ -180,9 +185,17 @@ class FusedPolicy:
         def bf16_bits(t):      # (rows, k) float tensor -> uint16 bit patterns, round to nearest even
             return t.to(torch.bfloat16).view(torch.int16).cpu().numpy().view(np.uint16)
 
-        def block(w, rows, k_pad):     # w: (out, in) -> [rows][k_pad + 8] bf16, zero padded
-            out = np.zeros((rows, k_pad + PAD), dtype=np.uint16)
-            out[: w.shape[0], : w.shape[1]] = bf16_bits(w)
+        def block(w, rows, k_pad):     # w: (out, in) -> one weight block of include/mbots_policy.h, zero padded
+            if layout == "rowpad":     # [rows][k_pad + 8] bf16
+                out = np.zeros((rows, k_pad + PAD), dtype=np.uint16)
+                out[: w.shape[0], : w.shape[1]] = bf16_bits(w)
+                return out
+            dense = np.zeros((H, H), dtype=np.uint16)
+            dense[: w.shape[0], : w.shape[1]] = bf16_bits(w)
+            row, k = np.meshgrid(np.arange(H), np.arange(H), indexing="ij")
+            ofs = (k // 64) * 16384 + (row // 8) * 1024 + (row % 8) * 128 + ((((k % 64) // 8) ^ (row % 8)) * 16) + (k % 8) * 2
+            out = np.zeros(H * H, dtype=np.uint16)      # K-major SWIZZLE_128B image, 32 KB
+            out[ofs.ravel() // 2] = dense.ravel()
             return out
 
         def f32(t):
@@ -242,6 +255,7 @@ class FusedPolicy:
             raise ValueError("network too deep for the fused kernel (12 ops)")
         self.program = _native.PolicyProgram()
         self.program.n_ops = len(ops)
+        self.program.layout = _native.LAYOUT_SW128 if layout == "sw128" else _native.LAYOUT_ROWPAD
         for i, (op, act, k_pad, w_ofs, b_ofs) in enumerate(ops):
             self.program.ops[i] = _native.PolicyOp(op, act, k_pad, w_ofs, b_ofs)
         host = np.frombuffer(b"".join(chunks), dtype=np.uint8).copy()
@@ -276,12 +290,13 @@ class PolicyRunner:
     """
 
     def __init__(self, sim, policies, seed=0, fused=False):
-        """fused=True: each species acts through one `mbots_policy_act` kernel (bf16 tensor cores) instead of
-        pack kernel + library GEMMs + sample kernel."""
+        """fused=True (or "sw128" / "rowpad", the FusedPolicy layout): each species acts through one
+        `mbots_policy_act` kernel (bf16 tensor cores) instead of pack kernel + library GEMMs + sample kernel."""
         if len(policies) != 4:
             raise ValueError("one policy per species (4)")
         self.sim, self.policies, self.seed = sim, policies, int(seed)
-        self.fused = [FusedPolicy(p) if not isinstance(p, FusedPolicy) else p for p in policies] if fused else None
+        layout = fused if isinstance(fused, str) else "sw128"
+        self.fused = [FusedPolicy(p, layout) if not isinstance(p, FusedPolicy) else p for p in policies] if fused else None
         self.draw = 0
 
     def species_blocks(self):

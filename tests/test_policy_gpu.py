@@ -166,9 +166,10 @@ def _bf16_reference_logits(pol, obs):
     return run(pol.actor, h)
 
 
+@pytest.mark.parametrize("layout", ["sw128", "rowpad"])
 @pytest.mark.parametrize("rtype,acts", [("GRU", ["Tanh", "ReLU"]), ("LSTM", ["LeakyReLU", "ReLU"]),
                                         ("RNN", ["LogSigmoid", "Tanh", "ELU"])])
-def test_fused_policy_kernel_matches_its_restatement(cuda_device, rtype, acts):
+def test_fused_policy_kernel_matches_its_restatement(cuda_device, rtype, acts, layout):
     import torch
     from madrona_bots import SimManager
     from madrona_bots.policy import FusedPolicy, SpeciesPolicy
@@ -179,7 +180,7 @@ def test_fused_policy_kernel_matches_its_restatement(cuda_device, rtype, acts):
         for p in net.parameters():
             p.mul_(2.0)
     pol = SpeciesPolicy(config, net.state_dict(), "cuda:0")
-    fused = FusedPolicy(pol)
+    fused = FusedPolicy(pol, layout)
     sim = SimManager(0, 40, 3, 32)
     _random_steps(sim, 5, 2)
     A = sim.num_agents()
@@ -207,12 +208,13 @@ def test_fused_policy_kernel_matches_its_restatement(cuda_device, rtype, acts):
     assert torch.equal(sim.action_tensor(False).to_torch(), before)
 
 
-def test_fused_policy_rejects_malformed_programs(cuda_device):
+@pytest.mark.parametrize("layout", ["sw128", "rowpad"])
+def test_fused_policy_rejects_malformed_programs(cuda_device, layout):
     import torch
     from madrona_bots import SimManager
     from madrona_bots.policy import FusedPolicy, SpeciesPolicy
     net, config = _make("RNN", ["Tanh"])
-    fused = FusedPolicy(SpeciesPolicy(config, net.state_dict(), "cuda:0"))
+    fused = FusedPolicy(SpeciesPolicy(config, net.state_dict(), "cuda:0"), layout)
     sim = SimManager(0, 4, 0, 32)
     sim.step()
     fused.program.ops[fused.program.n_ops - 1].w_ofs = fused.blob.numel()        # beyond the blob
@@ -221,9 +223,13 @@ def test_fused_policy_rejects_malformed_programs(cuda_device):
     fused.program.n_ops = 1
     with pytest.raises(RuntimeError, match="2..12 ops"):
         sim.policy_act(0, 8, fused, 0, 0)
+    fused.program.layout = 7
+    with pytest.raises(RuntimeError, match="unknown blob layout"):
+        sim.policy_act(0, 8, fused, 0, 0)
 
 
-def test_fused_policy_in_the_loop_matches_oracle(cuda_device):
+@pytest.mark.parametrize("layout", ["sw128", "rowpad"])
+def test_fused_policy_in_the_loop_matches_oracle(cuda_device, layout):
     import torch
     from madrona_bots.policy import PolicyRunner, SpeciesPolicy
     torch.manual_seed(1)
@@ -234,7 +240,7 @@ def test_fused_policy_in_the_loop_matches_oracle(cuda_device):
         pols.append(SpeciesPolicy(config, net.state_dict(), "cuda:0"))
     o, g = make_pair(32, 8, 32)
     o.step(); g.step()
-    runner = PolicyRunner(g, pols, seed=4, fused=True)
+    runner = PolicyRunner(g, pols, seed=4, fused=layout)
     for t in range(10):
         runner.act()
         act = g.action_tensor(False).to_torch()

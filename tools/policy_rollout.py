@@ -26,7 +26,8 @@ def main():
     ap.add_argument("--warmup", type=int, default=10)
     ap.add_argument("--universe", default=None)
     ap.add_argument("--dtype", default="fp32", choices=["fp32", "tf32", "bf16"])
-    ap.add_argument("--fused", action="store_true", help="one tensor-core kernel per species (mbots_policy_act)")
+    ap.add_argument("--fused", nargs="?", const="sw128", default=None, choices=["sw128", "rowpad"],
+                    help="one tensor-core kernel per species (mbots_policy_act): sw128 = tcgen05 kernel, rowpad = mma.sync kernel")
     a = ap.parse_args()
     if a.universe:
         pols = load_universe(a.universe, "cuda:0", dtype=a.dtype)
@@ -59,7 +60,7 @@ def main():
     out = {"worlds": a.worlds, "steps": a.steps, "agents": sim.num_agents(),
            "sim_ms_per_step": t_sim / a.steps, "policy_ms_per_step": t_pol / a.steps,
            "agent_steps_per_s": agent_steps / ((t_sim + t_pol) * 1e-3),
-           "policy": "universe_violence architectures, " + ("loaded" if a.universe else "random weights") + ", " + ("fused bf16 kernel" if a.fused else a.dtype)}
+           "policy": "universe_violence architectures, " + ("loaded" if a.universe else "random weights") + ", " + ("fused bf16 kernel (" + a.fused + ")" if a.fused else a.dtype)}
     print(json.dumps(out))
 
 
