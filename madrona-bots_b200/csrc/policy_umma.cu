@@ -3,13 +3,14 @@
  * Same contract as policy_fused.cu (one kernel per species: construct_obs -> species network -> softmax ->
  * Threefry sample -> one-hot action row), different engine: every layer is a 128 x N x K `tcgen05.mma` issued by
  * ONE thread, operands in shared memory in the canonical K-major SWIZZLE_128B layout, accumulator in tensor
- * memory. A persistent CTA per SM keeps TWO tiles of 128 agents in flight: while the four epilogue warps of one
+ * memory. A persistent CTA per SM keeps TWO tiles of 128 agents in flight: while the eight epilogue warps of one
  * tile pull its accumulator out of TMEM (tcgen05.ld: one thread = one agent row), apply bias / activation / gate
  * arithmetic and write the next layer's A operand back to shared memory (bf16, swizzled), the tensor core is
  * already multiplying the other tile. Weight blocks (bf16, pre-swizzled by the host, 32 KB each) arrive through a
  * three-deep ring of 1-D bulk copies (cp.async.bulk -> mbarrier complete_tx) issued by the MMA thread.
  *
- *   warps 0-3   epilogue of tile 0        warps 4-7   epilogue of tile 1        warp 8   lane 0: copies + MMA issue
+ *   warps 0-7   epilogue of tile 0        warps 8-15  epilogue of tile 1        warp 16  lane 0: copies + MMA issue
+ *               (warp & 3 = TMEM lane quarter = 32 agent rows, (warp >> 2) & 1 = which 64 of the 128 columns)
  *   mbarriers   w_full[3] / w_empty[3]    weight ring
  *               acc_full[2]               tcgen05.commit: accumulator of tile t is complete
  *               a_ready[2]                epilogue of tile t drained TMEM and (re)wrote its A operand
@@ -26,7 +27,8 @@ namespace mbk {
 
 constexpr int kUTile = 128;                         /* agents per tile = UMMA M */
 constexpr int kUBlockBytes = 128 * 128 * 2;          /* one operand: [128 rows][128 k] bf16 = two 16 KB K-blocks */
-constexpr int kUThreads = 288;                      /* 8 epilogue warps + 1 issue warp */
+constexpr int kUEpiWarps = 16;                      /* per tile: 4 TMEM lane quarters x 2 column halves */
+constexpr int kUThreads = (kUEpiWarps + 1) * 32;    /* + 1 issue warp */
 constexpr int kURing = 3;
 constexpr int kUTmemCols = 512;                     /* per tile: 128 accumulator columns + 128 scratch columns (x2 tiles, padded to 256 each) */
 
@@ -85,6 +87,14 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity)
         asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}"
                      : "=r"(done) : "r"(bar), "r"(parity) : "memory");
 }
+/* busy poll (no suspend window): for the issue warp, whose reaction time is on every tile's critical path */
+__device__ __forceinline__ void mbar_spin(uint32_t bar, uint32_t parity)
+{
+    uint32_t done = 0;
+    while (!done)
+        asm volatile("{\n\t.reg .pred p;\n\tmbarrier.test_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}"
+                     : "=r"(done) : "r"(bar), "r"(parity) : "memory");
+}
 __device__ __forceinline__ void bulk_copy_g2s(uint32_t dst, const void *src, uint32_t bytes, uint32_t bar)
 {
     asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
@@ -104,6 +114,10 @@ __device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&v)[32])
     asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
 }
 
+__device__ __forceinline__ void sts128(uint32_t addr, uint4 v)
+{
+    asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
+}
 __device__ __forceinline__ uint32_t upack_bf16(float lo, float hi)
 {
     const __nv_bfloat162 v = __floats2bfloat162_rn(lo, hi);
@@ -134,53 +148,132 @@ __device__ __forceinline__ float uact(float x)
     return x;
 }
 
-__device__ __forceinline__ void tmem_st32(uint32_t taddr, const uint32_t (&v)[32])
+/* 16 consecutive columns of this thread's TMEM lane; asynchronous until the matching wait. The waits take the
+ * destination registers as in/out operands so that no use of them can be scheduled ahead of the wait. */
+#define U16(v, q) q(v[0]), q(v[1]), q(v[2]), q(v[3]), q(v[4]), q(v[5]), q(v[6]), q(v[7]), q(v[8]), q(v[9]), q(v[10]), q(v[11]), q(v[12]), q(v[13]), q(v[14]), q(v[15])
+#define UQ_OUT(x) "=r"(x)
+#define UQ_IO(x) "+r"(x)
+#define UQ_IN(x) "r"(x)
+__device__ __forceinline__ void tmem_ld16(uint32_t taddr, uint32_t (&v)[16])
 {
-    asm volatile("tcgen05.st.sync.aligned.32x32b.x32.b32 [%0], "
-                 "{%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,%16,%17,%18,%19,%20,%21,%22,%23,%24,%25,%26,%27,%28,%29,%30,%31,%32};"
-                 ::"r"(taddr), "r"(v[0]), "r"(v[1]), "r"(v[2]), "r"(v[3]), "r"(v[4]), "r"(v[5]), "r"(v[6]), "r"(v[7]),
-                   "r"(v[8]), "r"(v[9]), "r"(v[10]), "r"(v[11]), "r"(v[12]), "r"(v[13]), "r"(v[14]), "r"(v[15]),
-                   "r"(v[16]), "r"(v[17]), "r"(v[18]), "r"(v[19]), "r"(v[20]), "r"(v[21]), "r"(v[22]), "r"(v[23]),
-                   "r"(v[24]), "r"(v[25]), "r"(v[26]), "r"(v[27]), "r"(v[28]), "r"(v[29]), "r"(v[30]), "r"(v[31])
-                 : "memory");
-    asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
+    asm volatile("tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];"
+                 : U16(v, UQ_OUT) : "r"(taddr) : "memory");
+}
+__device__ __forceinline__ void tmem_wait_ld(uint32_t (&v)[16])
+{
+    asm volatile("tcgen05.wait::ld.sync.aligned;" : U16(v, UQ_IO) :: "memory");
+}
+__device__ __forceinline__ void tmem_wait_ld(uint32_t (&v)[16], uint32_t (&s)[16])
+{
+    asm volatile("tcgen05.wait::ld.sync.aligned;" : U16(v, UQ_IO), U16(s, UQ_IO) :: "memory");
+}
+__device__ __forceinline__ void tmem_st16(uint32_t taddr, const uint32_t (&v)[16])
+{
+    asm volatile("tcgen05.st.sync.aligned.32x32b.x16.b32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,%16};"
+                 ::"r"(taddr), U16(v, UQ_IN) : "memory");
+}
+__device__ __forceinline__ void tmem_wait_st() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
+
+__device__ __forceinline__ bool elect_one()
+{
+    uint32_t p;
+    asm volatile("{\n\t.reg .pred P;\n\telect.sync _|P, 0xffffffff;\n\tselp.u32 %0, 1, 0, P;\n\t}" : "=r"(p));
+    return p != 0;
 }
 
-/* 32 activations of this thread's row -> four 16-byte chunks of the A operand */
-__device__ __forceinline__ void store_a_chunk(unsigned char *a_tile, uint32_t row, int c, const float (&x)[32])
+__device__ __forceinline__ void load_bias16(const float *bias, float (&b)[16])
 {
+    const float4 *p = reinterpret_cast<const float4 *>(bias);
 #pragma unroll
     for (int j = 0; j < 4; ++j) {
-        const uint4 p = make_uint4(upack_bf16(x[8 * j], x[8 * j + 1]), upack_bf16(x[8 * j + 2], x[8 * j + 3]),
-                                   upack_bf16(x[8 * j + 4], x[8 * j + 5]), upack_bf16(x[8 * j + 6], x[8 * j + 7]));
-        *reinterpret_cast<uint4 *>(a_tile + sw128_chunk_offset(row, (uint32_t)(c * 4 + j))) = p;
-    }
-}
-
-__device__ __forceinline__ void load_bias32(const float *bias, int c, float (&b)[32])
-{
-    const float4 *p = reinterpret_cast<const float4 *>(bias) + c * 8;
-#pragma unroll
-    for (int j = 0; j < 8; ++j) {
         const float4 v = __ldg(p + j);
         b[4 * j] = v.x; b[4 * j + 1] = v.y; b[4 * j + 2] = v.z; b[4 * j + 3] = v.w;
     }
 }
 
-template <int ACT>
-__device__ __forceinline__ void epi_linear(uint32_t acc, const float *bias, unsigned char *a_tile, uint32_t row)
+/* One weight block's epilogue for one thread: its row, 64 of the 128 columns, in four chunks of 16. The TMEM loads
+ * of chunk c + 1 are in flight while chunk c is computed; TMEM stores are waited for once, at the end. */
+enum { EM_LINEAR = 0, EM_LSTM_I, EM_LSTM_G, EM_LSTM_O, EM_GRU_R, EM_GRU_Z, EM_GRU_N };
+
+template <int MODE, int ACT>
+__device__ __forceinline__ void epi_block(uint32_t acc, uint32_t scratch, const float *bias, const float *bias_hn,
+                                          uint32_t a_tile, uint32_t row, int col_base)
 {
-#pragma unroll 1
-    for (int c = 0; c < 4; ++c) {
-        uint32_t v[32];
-        float b[32], x[32];
-        tmem_ld32(acc + (uint32_t)c * 32u, v);
-        load_bias32(bias, c, b);
+    constexpr bool kLoadScr = MODE == EM_LSTM_G || MODE == EM_LSTM_O || MODE == EM_GRU_Z || MODE == EM_GRU_N;
+    constexpr bool kStoreScr = MODE == EM_LSTM_I || MODE == EM_LSTM_G || MODE == EM_GRU_R || MODE == EM_GRU_Z;
+    uint32_t v[2][16], s[2][16];
+    tmem_ld16(acc + (uint32_t)col_base, v[0]);
+    if (kLoadScr) tmem_ld16(scratch + (uint32_t)col_base, s[0]);
 #pragma unroll
-        for (int i = 0; i < 32; ++i) x[i] = uact<ACT>(__uint_as_float(v[i]) + b[i]);
-        store_a_chunk(a_tile, row, c, x);
+    for (int c = 0; c < 4; ++c) {
+        const int cur = c & 1, col = col_base + c * 16;
+        float b[16];
+        load_bias16(bias + col, b);
+        if (kLoadScr) tmem_wait_ld(v[cur], s[cur]); else tmem_wait_ld(v[cur]);
+        if (c + 1 < 4) {
+            tmem_ld16(acc + (uint32_t)(col + 16), v[cur ^ 1]);
+            if (kLoadScr) tmem_ld16(scratch + (uint32_t)(col + 16), s[cur ^ 1]);
+        }
+        float x[16];
+        uint32_t out[16];
+        if (MODE == EM_GRU_R) {                                   /* park r * b_hn (low bf16 half) */
+            float hn[16];
+            load_bias16(bias_hn + col, hn);
+#pragma unroll
+            for (int i = 0; i < 16; ++i) out[i] = upack_bf16(usigmoid(__uint_as_float(v[cur][i]) + b[i]) * hn[i], 0.f);
+        }
+#pragma unroll
+        for (int i = 0; i < 16; ++i) {
+            const float pre = __uint_as_float(v[cur][i]) + b[i];
+            if (MODE == EM_LINEAR) x[i] = uact<ACT>(pre);
+            if (MODE == EM_LSTM_I) out[i] = __float_as_uint(usigmoid(pre));                                   /* sigmoid(i) */
+            if (MODE == EM_LSTM_G) out[i] = __float_as_uint(__uint_as_float(s[cur][i]) * utanh(pre));         /* c = sigmoid(i) tanh(g) */
+            if (MODE == EM_LSTM_O) x[i] = usigmoid(pre) * utanh(__uint_as_float(s[cur][i]));                  /* h = sigmoid(o) tanh(c) */
+            if (MODE == EM_GRU_Z) out[i] = upack_bf16(uunpack_bf16(s[cur][i]).x, 1.f - usigmoid(pre));        /* add 1 - z (high half) */
+            if (MODE == EM_GRU_N) {                                                                          /* h = (1 - z) tanh(n + b_in + r b_hn) */
+                const float2 rz = uunpack_bf16(s[cur][i]);
+                x[i] = rz.y * utanh(pre + rz.x);
+            }
+        }
+        if (kStoreScr) {
+            tmem_st16(scratch + (uint32_t)col, out);
+        } else {
+#pragma unroll
+            for (int j = 0; j < 2; ++j) {
+                const uint4 pk = make_uint4(upack_bf16(x[8 * j], x[8 * j + 1]), upack_bf16(x[8 * j + 2], x[8 * j + 3]),
+                                            upack_bf16(x[8 * j + 4], x[8 * j + 5]), upack_bf16(x[8 * j + 6], x[8 * j + 7]));
+                sts128(a_tile + sw128_chunk_offset(row, (uint32_t)((col >> 3) + j)), pk);
+            }
+        }
+    }
+    if (kStoreScr) tmem_wait_st();
+}
+
+template <int KS>
+__device__ __forceinline__ void issue_mmas(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc)
+{
+#pragma unroll
+    for (int ks = 0; ks < KS; ++ks) {                 /* k-step of 16: +32 B inside a 64-wide K-block, +16 KB to the next one */
+        const uint64_t off = (uint64_t)(((ks >> 2) * 16384 + (ks & 3) * 32) >> 4);
+        umma_bf16(tmem_d, adesc + off, bdesc + off, idesc, ks > 0 ? 1u : 0u);
     }
 }
+
+#ifdef MBK_UMMA_TRACE
+/* debug build only: a clock64 timeline of CTA 0 (tools/umma_trace.py); five actors (issuer, 4 epilogue lanes),
+ * each with its own region and a register counter: plain stores, no round trips */
+__device__ unsigned long long g_umma_trace[5 * 2 * 2048];
+#define UTRACE_DECL(actor_) uint32_t tr_n = 0; const uint32_t tr_actor = (actor_);
+#define UTRACE(code, t, b)                                                                                      \
+    if (blockIdx.x == 0 && tr_n < 2048) {                                                                       \
+        g_umma_trace[(tr_actor * 2048 + tr_n) * 2] = (code) | ((t) << 8) | ((uint32_t)(b) << 16) | 0x80000000u;  \
+        g_umma_trace[(tr_actor * 2048 + tr_n) * 2 + 1] = clock64();                                             \
+        ++tr_n;                                                                                                 \
+    }
+#else
+#define UTRACE_DECL(actor_)
+#define UTRACE(code, t, b)
+#endif
 
 struct UmmaPlan {                          /* weight blocks (32 KB each) in streaming order */
     int32_t n_blocks;
@@ -191,7 +284,7 @@ struct UmmaPlan {                          /* weight blocks (32 KB each) in stre
 
 struct UObsPtrs { const uint8_t *depth; const float *health; const float *position; const int8_t *semantic; const float *surrounding; };
 
-__global__ void __launch_bounds__(kUThreads, 1)
+__global__ void __launch_bounds__(kUThreads, 1)     /* 17 warps are allocated as 20: 96 registers per thread is the ceiling */
 policy_umma_kernel(UObsPtrs o, int32_t *__restrict__ action, uint32_t row_begin, uint32_t rows, const unsigned char *__restrict__ blob,
                    mbots_policy_program prog, UmmaPlan plan, uint32_t seed, uint32_t draw, int do_sample,
                    float *__restrict__ out_logits, int32_t *__restrict__ out_index)
@@ -200,7 +293,6 @@ policy_umma_kernel(UObsPtrs o, int32_t *__restrict__ action, uint32_t row_begin,
     unsigned char *smem = reinterpret_cast<unsigned char *>((reinterpret_cast<uintptr_t>(smem_raw) + 1023u) & ~(uintptr_t)1023u);
     const uint32_t smem_base = (uint32_t)__cvta_generic_to_shared(smem);
     const uint32_t w_base = smem_base, a_base = smem_base + kURing * kUBlockBytes, bar_base = a_base + 2 * kUBlockBytes;
-    unsigned char *a_ptr = smem + kURing * kUBlockBytes;
     uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(smem + (kURing + 2) * kUBlockBytes + 128);
     /* barriers: 8 bytes each */
     auto W_FULL = [&](int i) { return bar_base + (uint32_t)i * 8u; };
@@ -211,10 +303,10 @@ policy_umma_kernel(UObsPtrs o, int32_t *__restrict__ action, uint32_t row_begin,
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     if (tid == 0) {
         for (int i = 0; i < kURing; ++i) { mbar_init(W_FULL(i), 1); mbar_init(W_EMPTY(i), 1); }
-        for (int t = 0; t < 2; ++t) { mbar_init(ACC_FULL(t), 1); mbar_init(A_READY(t), 4); }
+        for (int t = 0; t < 2; ++t) { mbar_init(ACC_FULL(t), 1); mbar_init(A_READY(t), kUEpiWarps / 2); }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
-    if (warp == 8) {
+    if (warp == kUEpiWarps) {
         asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;"
                      ::"r"((uint32_t)__cvta_generic_to_shared(tmem_slot)), "r"((uint32_t)kUTmemCols) : "memory");
         asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
@@ -230,14 +322,15 @@ policy_umma_kernel(UObsPtrs o, int32_t *__restrict__ action, uint32_t row_begin,
     const uint32_t my_pairs = blockIdx.x < n_pairs ? (n_pairs - blockIdx.x + gridDim.x - 1) / gridDim.x : 0;
     const int B = plan.n_blocks;
 
-    if (warp < 8) {
-        /* ---------------- epilogue warps: thread = one agent row of tile t ---------------- */
-        const int t = warp >> 2, w4 = warp & 3;
+    if (warp < kUEpiWarps) {
+        /* ---------------- epilogue warps: thread = one agent row of tile t, half of its columns ---------------- */
+        const int t = warp >> 3, w4 = warp & 3, hf = (warp >> 2) & 1;
         const uint32_t r = (uint32_t)(w4 * 32 + lane);
-        unsigned char *a_tile = a_ptr + (size_t)t * kUBlockBytes;
+        const uint32_t a_tile = a_base + (uint32_t)t * kUBlockBytes;        /* shared-space address of this tile's A operand */
         const uint32_t acc = tmem + ((uint32_t)(w4 * 32) << 16) + (uint32_t)t * 256u, scratch = acc + 128u;
         const Key draw_key = key_split(key_init(seed), draw);
         uint32_t acc_phase = 0;
+        UTRACE_DECL(1 + t * 2 + hf)
         for (uint32_t it = 0; it < my_pairs; ++it) {
             const uint32_t tile = (blockIdx.x + it * gridDim.x) * 2u + (uint32_t)t;
             const size_t lr = (size_t)tile * kUTile + r;
@@ -267,7 +360,7 @@ policy_umma_kernel(UObsPtrs o, int32_t *__restrict__ action, uint32_t row_begin,
                 for (int j = 0; j < 10; ++j) {
                     const uint4 p = make_uint4(upack_bf16(x[8 * j], x[8 * j + 1]), upack_bf16(x[8 * j + 2], x[8 * j + 3]),
                                                upack_bf16(x[8 * j + 4], x[8 * j + 5]), upack_bf16(x[8 * j + 6], x[8 * j + 7]));
-                    *reinterpret_cast<uint4 *>(a_tile + sw128_chunk_offset(r, (uint32_t)j)) = p;
+                    if ((j >= 5) == (hf != 0)) sts128(a_tile + sw128_chunk_offset(r, (uint32_t)j), p);
                 }
             }
             fence_async_smem();
@@ -282,73 +375,32 @@ policy_umma_kernel(UObsPtrs o, int32_t *__restrict__ action, uint32_t row_begin,
                 mbar_wait(ACC_FULL(t), acc_phase);
                 acc_phase ^= 1u;
                 tc_fence_after();
+                if (lane == 0 && w4 == 0) { UTRACE(1, t, b) }
+                const int cb = hf * 64;
                 if (op.op == MBOTS_OP_LINEAR) {
                     switch (op.act) {
-                    case MBOTS_ACT_TANH: epi_linear<MBOTS_ACT_TANH>(acc, bias, a_tile, r); break;
-                    case MBOTS_ACT_ELU: epi_linear<MBOTS_ACT_ELU>(acc, bias, a_tile, r); break;
-                    case MBOTS_ACT_LOGSIGMOID: epi_linear<MBOTS_ACT_LOGSIGMOID>(acc, bias, a_tile, r); break;
-                    case MBOTS_ACT_LEAKYRELU: epi_linear<MBOTS_ACT_LEAKYRELU>(acc, bias, a_tile, r); break;
-                    case MBOTS_ACT_RELU: epi_linear<MBOTS_ACT_RELU>(acc, bias, a_tile, r); break;
-                    case MBOTS_ACT_SIGMOID: epi_linear<MBOTS_ACT_SIGMOID>(acc, bias, a_tile, r); break;
-                    default: epi_linear<MBOTS_ACT_NONE>(acc, bias, a_tile, r); break;
+                    case MBOTS_ACT_TANH: epi_block<EM_LINEAR, MBOTS_ACT_TANH>(acc, scratch, bias, bias, a_tile, r, cb); break;
+                    case MBOTS_ACT_ELU: epi_block<EM_LINEAR, MBOTS_ACT_ELU>(acc, scratch, bias, bias, a_tile, r, cb); break;
+                    case MBOTS_ACT_LOGSIGMOID: epi_block<EM_LINEAR, MBOTS_ACT_LOGSIGMOID>(acc, scratch, bias, bias, a_tile, r, cb); break;
+                    case MBOTS_ACT_LEAKYRELU: epi_block<EM_LINEAR, MBOTS_ACT_LEAKYRELU>(acc, scratch, bias, bias, a_tile, r, cb); break;
+                    case MBOTS_ACT_RELU: epi_block<EM_LINEAR, MBOTS_ACT_RELU>(acc, scratch, bias, bias, a_tile, r, cb); break;
+                    case MBOTS_ACT_SIGMOID: epi_block<EM_LINEAR, MBOTS_ACT_SIGMOID>(acc, scratch, bias, bias, a_tile, r, cb); break;
+                    default: epi_block<EM_LINEAR, MBOTS_ACT_NONE>(acc, scratch, bias, bias, a_tile, r, cb); break;
                     }
-                } else if (op.op == MBOTS_OP_LSTM0) {
-#pragma unroll 1
-                    for (int c = 0; c < 4; ++c) {
-                        uint32_t v[32], s[32];
-                        float bb[32];
-                        tmem_ld32(acc + (uint32_t)c * 32u, v);
-                        load_bias32(bias + gate * 128, c, bb);
-                        if (gate == 0) {                              /* i gate: park sigmoid(i) */
-#pragma unroll
-                            for (int i = 0; i < 32; ++i) s[i] = __float_as_uint(usigmoid(__uint_as_float(v[i]) + bb[i]));
-                            tmem_st32(scratch + (uint32_t)c * 32u, s);
-                        } else if (gate == 1) {                       /* g gate: c = sigmoid(i) * tanh(g) */
-                            tmem_ld32(scratch + (uint32_t)c * 32u, s);
-#pragma unroll
-                            for (int i = 0; i < 32; ++i) s[i] = __float_as_uint(__uint_as_float(s[i]) * utanh(__uint_as_float(v[i]) + bb[i]));
-                            tmem_st32(scratch + (uint32_t)c * 32u, s);
-                        } else {                                      /* o gate: h = sigmoid(o) * tanh(c) */
-                            float x[32];
-                            tmem_ld32(scratch + (uint32_t)c * 32u, s);
-#pragma unroll
-                            for (int i = 0; i < 32; ++i) x[i] = usigmoid(__uint_as_float(v[i]) + bb[i]) * utanh(__uint_as_float(s[i]));
-                            store_a_chunk(a_tile, r, c, x);
-                        }
-                    }
+                } else if (op.op == MBOTS_OP_LSTM0) {                 /* biases: b_i, b_g, b_o */
+                    const float *bg = bias + gate * 128;
+                    if (gate == 0) epi_block<EM_LSTM_I, 0>(acc, scratch, bg, bg, a_tile, r, cb);
+                    else if (gate == 1) epi_block<EM_LSTM_G, 0>(acc, scratch, bg, bg, a_tile, r, cb);
+                    else epi_block<EM_LSTM_O, 0>(acc, scratch, bg, bg, a_tile, r, cb);
                 } else if (op.op == MBOTS_OP_GRU0) {                  /* biases: b_r, b_z, b_in, b_hn */
-#pragma unroll 1
-                    for (int c = 0; c < 4; ++c) {
-                        uint32_t v[32], s[32];
-                        float bb[32];
-                        tmem_ld32(acc + (uint32_t)c * 32u, v);
-                        load_bias32(bias + gate * 128, c, bb);
-                        if (gate == 0) {                              /* r gate: park r * b_hn (low bf16 half) */
-                            float hn[32];
-                            load_bias32(bias + 3 * 128, c, hn);
-#pragma unroll
-                            for (int i = 0; i < 32; ++i) s[i] = upack_bf16(usigmoid(__uint_as_float(v[i]) + bb[i]) * hn[i], 0.f);
-                            tmem_st32(scratch + (uint32_t)c * 32u, s);
-                        } else if (gate == 1) {                       /* z gate: add 1 - z (high bf16 half) */
-                            tmem_ld32(scratch + (uint32_t)c * 32u, s);
-#pragma unroll
-                            for (int i = 0; i < 32; ++i) s[i] = upack_bf16(uunpack_bf16(s[i]).x, 1.f - usigmoid(__uint_as_float(v[i]) + bb[i]));
-                            tmem_st32(scratch + (uint32_t)c * 32u, s);
-                        } else {                                      /* n gate: h = (1 - z) * tanh(n + b_in + r * b_hn) */
-                            float x[32];
-                            tmem_ld32(scratch + (uint32_t)c * 32u, s);
-#pragma unroll
-                            for (int i = 0; i < 32; ++i) {
-                                const float2 rz = uunpack_bf16(s[i]);
-                                x[i] = rz.y * utanh(__uint_as_float(v[i]) + bb[i] + rz.x);
-                            }
-                            store_a_chunk(a_tile, r, c, x);
-                        }
-                    }
+                    const float *bg = bias + gate * 128;
+                    if (gate == 0) epi_block<EM_GRU_R, 0>(acc, scratch, bg, bias + 3 * 128, a_tile, r, cb);
+                    else if (gate == 1) epi_block<EM_GRU_Z, 0>(acc, scratch, bg, bg, a_tile, r, cb);
+                    else epi_block<EM_GRU_N, 0>(acc, scratch, bg, bg, a_tile, r, cb);
                 } else {                                              /* HEAD: 6 logits in columns 0..5 */
-                    uint32_t v[32];
-                    tmem_ld32(acc, v);
-                    if (live) {
+                    uint32_t v[16];
+                    if (hf == 0) { tmem_ld16(acc, v); tmem_wait_ld(v); }
+                    if (live && hf == 0) {
                         float l[6];
 #pragma unroll
                         for (int k = 0; k < 6; ++k) l[k] = __uint_as_float(v[k]) + __ldg(bias + k);
@@ -369,58 +421,74 @@ policy_umma_kernel(UObsPtrs o, int32_t *__restrict__ action, uint32_t row_begin,
                     }
                 }
                 if (b + 1 < B) {          /* accumulator drained, A operand (re)written: the next block may be issued */
+                    if (lane == 0 && w4 == 0) { UTRACE(3, t, b) }
                     fence_async_smem();
                     tc_fence_before();
                     __syncwarp();
+                    if (lane == 0 && w4 == 0) { UTRACE(5, t, b) }
                     if (lane == 0) mbar_arrive(A_READY(t));
                 }
             }
         }
     } else {
-        if (lane == 0) {
-        /* ---------------- issue thread: weight ring + tcgen05.mma ---------------- */
+        /* ---------------- issue warp: weight ring + tcgen05.mma. Every lane runs the (warp-uniform) control flow,
+         * one elected lane issues the copies, the products and the commits ---------------- */
         const uint32_t total = my_pairs * (uint32_t)B;
-        auto fetch = [&](uint32_t g) {     /* global block number g -> ring slot g % 3 */
-            if (g < total) {
-                const uint32_t slot = g % kURing;
-                mbar_expect_tx(W_FULL(slot), kUBlockBytes);
-                bulk_copy_g2s(w_base + slot * kUBlockBytes, blob + plan.ofs[g % (uint32_t)B], kUBlockBytes, W_FULL(slot));
+        uint32_t f_g = 0, f_b = 0, f_slot = 0;                        /* next block to fetch: number, index in the program, ring slot */
+        auto fetch = [&]() {
+            if (f_g < total) {
+                if (elect_one()) {
+                    mbar_expect_tx(W_FULL(f_slot), kUBlockBytes);
+                    bulk_copy_g2s(w_base + f_slot * kUBlockBytes, blob + plan.ofs[f_b], kUBlockBytes, W_FULL(f_slot));
+                }
+                ++f_g;
+                if (++f_b == (uint32_t)B) f_b = 0;
+                if (++f_slot == (uint32_t)kURing) f_slot = 0;
             }
         };
-        for (uint32_t g = 0; g < (uint32_t)kURing; ++g) fetch(g);
-        uint32_t a_phase[2] = {0u, 0u};
-        uint32_t g = 0;
+        for (int i = 0; i < kURing; ++i) fetch();
+        uint32_t a_phase = 0, slot = 0, w_phase = 0, prev_slot = 0, prev_phase = 0;
+        bool first = true;
+        UTRACE_DECL(0)
         for (uint32_t it = 0; it < my_pairs; ++it) {
-            for (int b = 0; b < B; ++b, ++g) {
-                const uint32_t slot = g % kURing;
+            for (int b = 0; b < B; ++b) {
                 const mbots_policy_op op = prog.ops[plan.op_of[b]];
-                const uint32_t ksteps = op.k_pad >> 4;
                 const uint32_t idesc = umma_idesc(op.op == MBOTS_OP_HEAD ? 16u : 128u);
-                mbar_wait(W_FULL(slot), (g / kURing) & 1u);
+                const uint64_t bdesc = umma_desc(w_base + slot * kUBlockBytes);
+                mbar_wait(W_FULL(slot), w_phase);
+                if (lane == 0) { UTRACE(10, 0, b) }
+#pragma unroll
                 for (int t = 0; t < 2; ++t) {
-                    mbar_wait(A_READY(t), a_phase[t]);
-                    a_phase[t] ^= 1u;
+                    mbar_spin(A_READY(t), a_phase);
+                    if (lane == 0) { UTRACE(11, t, b) }
                     tc_fence_after();
-                    const uint32_t a0 = a_base + (uint32_t)t * kUBlockBytes, b0 = w_base + slot * kUBlockBytes;
-                    for (uint32_t ks = 0; ks < ksteps; ++ks) {
-                        const uint32_t off = (ks >> 2) * 16384u + (ks & 3u) * 32u;
-                        umma_bf16(tmem + (uint32_t)t * 256u, umma_desc(a0 + off), umma_desc(b0 + off), idesc, ks > 0 ? 1u : 0u);
+                    const uint64_t adesc = umma_desc(a_base + (uint32_t)t * kUBlockBytes);
+                    if (elect_one()) {
+                        if (op.k_pad == 80u) issue_mmas<5>(tmem + (uint32_t)t * 256u, adesc, bdesc, idesc);
+                        else issue_mmas<8>(tmem + (uint32_t)t * 256u, adesc, bdesc, idesc);
+                        umma_commit(ACC_FULL(t));
                     }
-                    umma_commit(ACC_FULL(t));
+                    __syncwarp();
+                    if (lane == 0) { UTRACE(12, t, b) }
                 }
-                umma_commit(W_EMPTY(slot));
-                if (g >= 1) {              /* the slot of block g - 1 is free once its products are done: refill it */
-                    mbar_wait(W_EMPTY((g - 1) % kURing), ((g - 1) / kURing) & 1u);
-                    fetch(g + 2);
+                a_phase ^= 1u;
+                if (elect_one()) umma_commit(W_EMPTY(slot));
+                __syncwarp();
+                if (!first) {              /* the slot of the previous block is free once its products are done: refill it */
+                    mbar_wait(W_EMPTY(prev_slot), prev_phase);
+                    if (lane == 0) { UTRACE(13, 0, b) }
+                    fetch();
                 }
+                first = false;
+                prev_slot = slot;
+                prev_phase = w_phase;
+                if (++slot == (uint32_t)kURing) { slot = 0; w_phase ^= 1u; }
             }
         }
-        }
-        __syncwarp();
     }
     tc_fence_before();
     __syncthreads();
-    if (warp == 8) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"((uint32_t)kUTmemCols) : "memory");
+    if (warp == kUEpiWarps) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"((uint32_t)kUTmemCols) : "memory");
 }
 
 /* Host: validate a SW128-layout program against the blob and derive the streaming plan. Returns 0 or a message. */
@@ -475,3 +543,13 @@ const char *launch_policy_umma(const ObsSet &o, uint32_t row_begin, uint32_t row
 }
 
 } // namespace mbk
+
+#ifdef MBK_UMMA_TRACE
+extern "C" int mbots_debug_umma_trace(unsigned long long *out, int reset)
+{
+    cudaDeviceSynchronize();
+    if (out) cudaMemcpyFromSymbol(out, mbk::g_umma_trace, sizeof(mbk::g_umma_trace));
+    if (reset) { void *p = nullptr; cudaGetSymbolAddress(&p, mbk::g_umma_trace); cudaMemset(p, 0, sizeof(mbk::g_umma_trace)); }
+    return 0;
+}
+#endif
