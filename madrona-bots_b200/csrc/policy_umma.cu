@@ -33,7 +33,8 @@ constexpr int kURing = 3;
 constexpr int kUTmemCols = 512;                     /* per tile: 128 accumulator columns + 128 scratch columns (x2 tiles, padded to 256 each) */
 
 /* shared memory: [weights x3][A operand x2] + barriers (1 KB aligned base) */
-constexpr int kUSmemBytes = (kURing + 2) * kUBlockBytes + 1024 /* alignment slack */ + 256 /* barriers */;
+constexpr int kUBiasFloats = MBOTS_POLICY_MAX_OPS * 512;      /* every bias vector of the program, staged once per CTA */
+constexpr int kUSmemBytes = (kURing + 2) * kUBlockBytes + 1024 /* alignment slack */ + 256 /* barriers */ + kUBiasFloats * 4;
 size_t policy_umma_smem_bytes() { return kUSmemBytes; }
 
 /* byte offset of (row, k) in a K-major SWIZZLE_128B operand: K-blocks of 64, 8-row atoms of 1024 B, 16-byte
@@ -181,14 +182,12 @@ __device__ __forceinline__ bool elect_one()
     return p != 0;
 }
 
-__device__ __forceinline__ void load_bias16(const float *bias, float (&b)[16])
+__device__ __forceinline__ void load_bias16(uint32_t bias /* shared-space address */, float (&b)[16])
 {
-    const float4 *p = reinterpret_cast<const float4 *>(bias);
 #pragma unroll
-    for (int j = 0; j < 4; ++j) {
-        const float4 v = __ldg(p + j);
-        b[4 * j] = v.x; b[4 * j + 1] = v.y; b[4 * j + 2] = v.z; b[4 * j + 3] = v.w;
-    }
+    for (int j = 0; j < 4; ++j)
+        asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];"
+                     : "=f"(b[4 * j]), "=f"(b[4 * j + 1]), "=f"(b[4 * j + 2]), "=f"(b[4 * j + 3]) : "r"(bias + 16u * j));
 }
 
 /* One weight block's epilogue for one thread: its row, 64 of the 128 columns, in four chunks of 16. The TMEM loads
@@ -196,29 +195,31 @@ __device__ __forceinline__ void load_bias16(const float *bias, float (&b)[16])
 enum { EM_LINEAR = 0, EM_LSTM_I, EM_LSTM_G, EM_LSTM_O, EM_GRU_R, EM_GRU_Z, EM_GRU_N };
 
 template <int MODE, int ACT>
-__device__ __forceinline__ void epi_block(uint32_t acc, uint32_t scratch, const float *bias, const float *bias_hn,
+__device__ __forceinline__ void epi_block(uint32_t acc, uint32_t scratch, uint32_t bias, uint32_t bias_hn,
                                           uint32_t a_tile, uint32_t row, int col_base)
 {
     constexpr bool kLoadScr = MODE == EM_LSTM_G || MODE == EM_LSTM_O || MODE == EM_GRU_Z || MODE == EM_GRU_N;
     constexpr bool kStoreScr = MODE == EM_LSTM_I || MODE == EM_LSTM_G || MODE == EM_GRU_R || MODE == EM_GRU_Z;
     uint32_t v[2][16], s[2][16];
+    float bb[2][16];
     tmem_ld16(acc + (uint32_t)col_base, v[0]);
     if (kLoadScr) tmem_ld16(scratch + (uint32_t)col_base, s[0]);
+    load_bias16(bias + 4u * col_base, bb[0]);
 #pragma unroll
     for (int c = 0; c < 4; ++c) {
         const int cur = c & 1, col = col_base + c * 16;
-        float b[16];
-        load_bias16(bias + col, b);
+        const float (&b)[16] = bb[cur];
         if (kLoadScr) tmem_wait_ld(v[cur], s[cur]); else tmem_wait_ld(v[cur]);
         if (c + 1 < 4) {
             tmem_ld16(acc + (uint32_t)(col + 16), v[cur ^ 1]);
             if (kLoadScr) tmem_ld16(scratch + (uint32_t)(col + 16), s[cur ^ 1]);
+            load_bias16(bias + 4u * (col + 16), bb[cur ^ 1]);
         }
         float x[16];
         uint32_t out[16];
         if (MODE == EM_GRU_R) {                                   /* park r * b_hn (low bf16 half) */
             float hn[16];
-            load_bias16(bias_hn + col, hn);
+            load_bias16(bias_hn + 4u * col, hn);
 #pragma unroll
             for (int i = 0; i < 16; ++i) out[i] = upack_bf16(usigmoid(__uint_as_float(v[cur][i]) + b[i]) * hn[i], 0.f);
         }
@@ -280,6 +281,8 @@ struct UmmaPlan {                          /* weight blocks (32 KB each) in stre
     uint32_t ofs[3 * MBOTS_POLICY_MAX_OPS];
     uint8_t op_of[3 * MBOTS_POLICY_MAX_OPS];
     uint8_t gate_of[3 * MBOTS_POLICY_MAX_OPS];
+    uint16_t bias_at[MBOTS_POLICY_MAX_OPS];   /* float offset of each op's biases in the shared-memory copy */
+    uint16_t bias_n[MBOTS_POLICY_MAX_OPS];
 };
 
 struct UObsPtrs { const uint8_t *depth; const float *health; const float *position; const int8_t *semantic; const float *surrounding; };
@@ -310,6 +313,12 @@ policy_umma_kernel(UObsPtrs o, int32_t *__restrict__ action, uint32_t row_begin,
         asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;"
                      ::"r"((uint32_t)__cvta_generic_to_shared(tmem_slot)), "r"((uint32_t)kUTmemCols) : "memory");
         asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    float *bias_s = reinterpret_cast<float *>(smem + (kURing + 2) * kUBlockBytes + 256);
+    const uint32_t bias_base = bar_base + 256u;
+    for (int i = 0; i < prog.n_ops; ++i) {
+        const float *src = reinterpret_cast<const float *>(blob + prog.ops[i].b_ofs);
+        for (int j = tid; j < plan.bias_n[i]; j += kUThreads) bias_s[plan.bias_at[i] + j] = __ldg(src + j);
     }
     tc_fence_before();
     __syncthreads();
@@ -371,7 +380,7 @@ policy_umma_kernel(UObsPtrs o, int32_t *__restrict__ action, uint32_t row_begin,
             for (int b = 0; b < B; ++b) {
                 const mbots_policy_op op = prog.ops[plan.op_of[b]];
                 const int gate = plan.gate_of[b];
-                const float *bias = reinterpret_cast<const float *>(blob + op.b_ofs);
+                const uint32_t bias = bias_base + 4u * plan.bias_at[plan.op_of[b]];
                 mbar_wait(ACC_FULL(t), acc_phase);
                 acc_phase ^= 1u;
                 tc_fence_after();
@@ -388,13 +397,13 @@ policy_umma_kernel(UObsPtrs o, int32_t *__restrict__ action, uint32_t row_begin,
                     default: epi_block<EM_LINEAR, MBOTS_ACT_NONE>(acc, scratch, bias, bias, a_tile, r, cb); break;
                     }
                 } else if (op.op == MBOTS_OP_LSTM0) {                 /* biases: b_i, b_g, b_o */
-                    const float *bg = bias + gate * 128;
+                    const uint32_t bg = bias + 512u * (uint32_t)gate;
                     if (gate == 0) epi_block<EM_LSTM_I, 0>(acc, scratch, bg, bg, a_tile, r, cb);
                     else if (gate == 1) epi_block<EM_LSTM_G, 0>(acc, scratch, bg, bg, a_tile, r, cb);
                     else epi_block<EM_LSTM_O, 0>(acc, scratch, bg, bg, a_tile, r, cb);
                 } else if (op.op == MBOTS_OP_GRU0) {                  /* biases: b_r, b_z, b_in, b_hn */
-                    const float *bg = bias + gate * 128;
-                    if (gate == 0) epi_block<EM_GRU_R, 0>(acc, scratch, bg, bias + 3 * 128, a_tile, r, cb);
+                    const uint32_t bg = bias + 512u * (uint32_t)gate;
+                    if (gate == 0) epi_block<EM_GRU_R, 0>(acc, scratch, bg, bias + 3u * 512u, a_tile, r, cb);
                     else if (gate == 1) epi_block<EM_GRU_Z, 0>(acc, scratch, bg, bg, a_tile, r, cb);
                     else epi_block<EM_GRU_N, 0>(acc, scratch, bg, bg, a_tile, r, cb);
                 } else {                                              /* HEAD: 6 logits in columns 0..5 */
@@ -403,7 +412,7 @@ policy_umma_kernel(UObsPtrs o, int32_t *__restrict__ action, uint32_t row_begin,
                     if (live && hf == 0) {
                         float l[6];
 #pragma unroll
-                        for (int k = 0; k < 6; ++k) l[k] = __uint_as_float(v[k]) + __ldg(bias + k);
+                        for (int k = 0; k < 6; ++k) l[k] = __uint_as_float(v[k]) + bias_s[plan.bias_at[plan.op_of[b]] + k];
                         if (out_logits) {
 #pragma unroll
                             for (int k = 0; k < 6; ++k) out_logits[lr * 6 + k] = l[k];
@@ -509,6 +518,8 @@ static const char *policy_umma_plan(const mbots_policy_program &p, uint64_t blob
         const uint32_t nbias = op.op == MBOTS_OP_HEAD ? 8u : op.op == MBOTS_OP_GRU0 ? 4u * 128u : blocks * 128u;
         if ((uint64_t)op.w_ofs + (uint64_t)blocks * kUBlockBytes > blob_bytes || (uint64_t)op.b_ofs + 4ull * nbias > blob_bytes)
             return "op reaches beyond the blob";
+        plan.bias_at[i] = (uint16_t)(i * 512);
+        plan.bias_n[i] = (uint16_t)nbias;
         for (uint32_t j = 0; j < blocks; ++j) {
             plan.ofs[plan.n_blocks] = op.w_ofs + j * (uint32_t)kUBlockBytes;
             plan.op_of[plan.n_blocks] = (uint8_t)i;
@@ -523,7 +534,7 @@ const char *launch_policy_umma(const ObsSet &o, uint32_t row_begin, uint32_t row
                                const mbots_policy_program &prog, uint32_t seed, uint32_t draw, int do_sample,
                                float *out_logits, int32_t *out_index, cudaStream_t s)
 {
-    UmmaPlan plan;
+    UmmaPlan plan = {};
     const char *err = policy_umma_plan(prog, blob_bytes, plan);
     if (err || rows == 0) return err;
     if (reinterpret_cast<uintptr_t>(blob) & 15u) return "the blob must be 16-byte aligned";
