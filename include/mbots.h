@@ -201,7 +201,9 @@ int mbots_sample_actions(mbots_sim *sim, uint32_t row_begin, uint32_t row_end, c
 /* The whole acting path of learn/training_loop.py:52-83,136 for rows [row_begin, row_end) as ONE kernel:
  * construct_obs -> species network (mbots_policy.h program over a device blob of bf16 weights) -> softmax ->
  * Categorical sample (same stream as mbots_sample_actions: keyed seed, draw, row) -> one-hot row in the action
- * export. Tensor-core products (bf16 in, fp32 accumulate); activations stay in registers between layers.
+ * export. Tensor-core products (bf16 in, fp32 accumulate); activations never leave the SM between layers.
+ * program->layout picks the kernel: MBOTS_LAYOUT_SW128 = tcgen05.mma + tensor memory (policy_umma.cu),
+ * MBOTS_LAYOUT_ROWPAD = mma.sync (policy_fused.cu); the blob must be laid out accordingly (mbots_policy.h).
  * sample = 0 skips sampling and the action write (use out_logits). out_logits: device (n, 6) float32 or NULL;
  * out_index: device (n) int32 or NULL. Asynchronous on `stream`. MBOTS_EINVAL for a malformed program. */
 int mbots_policy_act(mbots_sim *sim, uint32_t row_begin, uint32_t row_end, const void *blob, uint64_t blob_bytes,
