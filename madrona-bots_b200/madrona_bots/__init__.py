@@ -210,9 +210,13 @@ class SimManager:
         _native.check(self._lib.mbots_copy_from_host(self._h, EXPORT[name], ctypes.c_void_p(host_ptr), nbytes,
                                                      self._stream()), "mbots_copy_from_host")
 
-    def copy_to_host(self, name, host_ptr, nbytes):
-        _native.check(self._lib.mbots_copy_to_host(self._h, EXPORT[name], ctypes.c_void_p(host_ptr), nbytes,
-                                                   self._stream()), "mbots_copy_to_host")
+    def copy_to_host(self, name, host_ptr, nbytes, stream=None):
+        """Asynchronous on `stream` (a torch.cuda.Stream; default: the current stream). The exports of a step stay
+        intact until the step after next (double-buffered row sets), so a copy stream that waits on an event
+        recorded after step t may drain them while step t + 1 runs -- as long as step t + 2 waits for the copy."""
+        st = self._stream() if stream is None else ctypes.c_void_p(stream.cuda_stream)
+        _native.check(self._lib.mbots_copy_to_host(self._h, EXPORT[name], ctypes.c_void_p(host_ptr), nbytes, st),
+                      "mbots_copy_to_host")
 
     # ---- policy-inference ends (SURVEY section 8(f) item 1) --------------------------------
     def pack_observations(self, start, end, prev=False, out=None):
