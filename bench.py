@@ -213,7 +213,7 @@ def run_reference(args, rank, world):
 
 def workload_config(args, sample=None):
     c = {"workload": f"{args.worlds_per_gpu} worlds x {INIT_AGENTS} initial agents per GPU, random one-hot actions, "
-                     "step + sensor + shift_observations per step",
+                     "step + sensor + shift_observations per step, one host synchronisation per step",
          "worlds_per_gpu": args.worlds_per_gpu, "init_agents_per_world": INIT_AGENTS, "seed": SEED,
          "sharding": f"worlds x{args.gpus} (independent worlds, no data-path collective)",
          "l2": "per-step working set (~1.5 GB at 65,536 worlds) exceeds the 126 MB L2; no explicit flush"}
@@ -300,8 +300,9 @@ def run_ours(args, rank, world, local_rank):
         A = sim.num_agents()
         assert A <= rows_cap, "action pool too small for the population"
         sim.action_tensor(False).to_torch().copy_(dev_pool[i % POOL][:A])
-        sim.step()
+        sim.step_async()
         sim.shift_observations_async()
+        sim.sync()                                    # one host synchronisation per step (the next step needs the row count)
 
     # ---------------- device-resident leg (value) ----------------
     for i in range(args.warmup):

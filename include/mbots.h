@@ -122,6 +122,9 @@ int mbots_step(mbots_sim *sim, void *stream);
 /* Same work, enqueued only (no host synchronisation). mbots_num_agents() and the
  * dims reported by mbots_tensor() are stale until mbots_sync(). */
 int mbots_step_async(mbots_sim *sim, void *stream);
+/* Blocks until the last enqueued step is complete (exports written, counts on the host). Work queued behind that
+ * step on the stream -- e.g. an asynchronous shift -- is not waited for: step_async, shift_observations_async,
+ * sync lets the shift run while the host prepares the next step. */
 int mbots_sync(mbots_sim *sim, void *stream);
 
 /* Manager::shiftObservations (src/entry/mgr.cpp:194-197). Blocking. */

@@ -48,7 +48,9 @@ struct mbots_sim {
     /* per-kernel timing */
     bool profile;
     cudaEvent_t ev[5], evShift[2];
+    cudaEvent_t evTotals;          /* recorded behind the step's last kernel and the copy of the totals */
     bool shiftPending;             /* evShift recorded, elapsed time not read yet */
+    bool stepPending;              /* ev[0..3] recorded, elapsed times not read yet */
     double ms[K_COUNT];
     uint32_t calls[K_COUNT];
 };
@@ -132,12 +134,15 @@ void free_all(mbots_sim *s)
     if (s->hStats) cudaFreeHost(s->hStats);
     for (auto &e : s->ev) if (e) cudaEventDestroy(e);
     for (auto &e : s->evShift) if (e) cudaEventDestroy(e);
+    if (s->evTotals) cudaEventDestroy(s->evTotals);
 }
 
-/* the shift kernel's events are read lazily so that profiling does not make the asynchronous shift blocking */
-void resolve_shift_timing(mbots_sim *s)
+/* Kernel timing events are read lazily so that profiling never turns an asynchronous call into a blocking one:
+ * `wait` = false reads them only if they have completed (the read is retried later), true blocks for them. */
+void resolve_shift_timing(mbots_sim *s, bool wait = true)
 {
     if (!s->shiftPending) return;
+    if (!wait && cudaEventQuery(s->evShift[1]) != cudaSuccess) return;
     s->shiftPending = false;
     float a = 0;
     if (cudaEventSynchronize(s->evShift[1]) == cudaSuccess &&
@@ -146,10 +151,27 @@ void resolve_shift_timing(mbots_sim *s)
     }
 }
 
+void resolve_step_timing(mbots_sim *s)
+{
+    if (!s->stepPending) return;
+    s->stepPending = false;
+    float a = 0, b = 0, c = 0;
+    if (cudaEventSynchronize(s->ev[3]) != cudaSuccess) return;
+    cudaEventElapsedTime(&a, s->ev[0], s->ev[1]);
+    cudaEventElapsedTime(&b, s->ev[1], s->ev[2]);
+    cudaEventElapsedTime(&c, s->ev[2], s->ev[3]);
+    s->ms[K_STEP] += a; s->ms[K_SCAN] += b; s->ms[K_EXPORT] += c;
+    s->calls[K_STEP]++; s->calls[K_SCAN]++; s->calls[K_EXPORT]++;
+}
+
+/* Wait for the last enqueued step (its exports and the host copy of the totals), not for work queued behind it:
+ * a shift enqueued before the sync keeps running while the host prepares the next step. */
 int finish(mbots_sim *s, cudaStream_t st)
 {
-    CU(cudaStreamSynchronize(st));
-    resolve_shift_timing(s);
+    (void)st;
+    CU(cudaEventSynchronize(s->evTotals));
+    resolve_step_timing(s);                 /* complete by now */
+    resolve_shift_timing(s, false);         /* a shift queued behind the step may still be running */
     s->totalAgents = s->hTotals->totalAgents;
     s->dirty = false;
     return MBOTS_OK;
@@ -163,6 +185,7 @@ int enqueue_repack(mbots_sim *s, cudaStream_t st, int with_sensors, int count_st
     if (s->profile && with_sensors) cudaEventRecord(s->ev[3], st);
     CU(cudaGetLastError());
     CU(cudaMemcpyAsync(s->hTotals, s->d.totals, sizeof(Totals), cudaMemcpyDeviceToHost, st));
+    CU(cudaEventRecord(s->evTotals, st));
     s->cur ^= 1;
     s->launches += 2 + (uint64_t)nexp;                  /* tile sums, row scan, export variant(s) */
     s->dirty = true;
@@ -171,7 +194,7 @@ int enqueue_repack(mbots_sim *s, cudaStream_t st, int with_sensors, int count_st
 
 int enqueue_step(mbots_sim *s, cudaStream_t st)
 {
-    if (s->profile) cudaEventRecord(s->ev[0], st);
+    if (s->profile) { resolve_step_timing(s); cudaEventRecord(s->ev[0], st); }
     /* block size: the largest world known from the last synchronised step (rounded to a warp), or
      * the capacity when counts are stale because steps were enqueued without a sync in between */
     uint32_t threads = s->d.cap, bound = 0;
@@ -189,15 +212,7 @@ int enqueue_step(mbots_sim *s, cudaStream_t st)
     s->launches += 1;
     int rc = enqueue_repack(s, st, 1, 1, bound);
     if (rc != MBOTS_OK) return rc;
-    if (s->profile) {
-        CU(cudaEventSynchronize(s->ev[3]));
-        float a = 0, b = 0, c = 0;
-        cudaEventElapsedTime(&a, s->ev[0], s->ev[1]);
-        cudaEventElapsedTime(&b, s->ev[1], s->ev[2]);
-        cudaEventElapsedTime(&c, s->ev[2], s->ev[3]);
-        s->ms[K_STEP] += a; s->ms[K_SCAN] += b; s->ms[K_EXPORT] += c;
-        s->calls[K_STEP]++; s->calls[K_SCAN]++; s->calls[K_EXPORT]++;
-    }
+    if (s->profile) s->stepPending = true;
     return MBOTS_OK;
 }
 
@@ -244,6 +259,7 @@ int mbots_create_ex(const mbots_config *cfg, mbots_sim **out)
     if (rc == MBOTS_OK) {
         for (auto &ev : s->ev) if (cudaEventCreate(&ev) != cudaSuccess) rc = fail(MBOTS_ECUDA, "cudaEventCreate");
         for (auto &ev : s->evShift) if (cudaEventCreate(&ev) != cudaSuccess) rc = fail(MBOTS_ECUDA, "cudaEventCreate");
+        if (cudaEventCreateWithFlags(&s->evTotals, cudaEventDisableTiming) != cudaSuccess) rc = fail(MBOTS_ECUDA, "cudaEventCreate");
     }
     if (rc == MBOTS_OK) {
         size_t sm1 = step_smem_bytes(cap), sm2 = export_smem_bytes(cap, 8, false);
@@ -475,6 +491,7 @@ int mbots_launch_count(mbots_sim *s, uint64_t *out)
 int mbots_profile(mbots_sim *s, int32_t enable)
 {
     if (!s) return fail(MBOTS_EINVAL, "null handle");
+    resolve_step_timing(s);
     resolve_shift_timing(s);
     s->profile = enable != 0;
     for (int i = 0; i < K_COUNT; ++i) { s->ms[i] = 0; s->calls[i] = 0; }
@@ -484,6 +501,7 @@ int mbots_profile(mbots_sim *s, int32_t enable)
 int mbots_profile_read(mbots_sim *s, float out_ms[4], uint32_t out_calls[4])
 {
     if (!s || !out_ms || !out_calls) return fail(MBOTS_EINVAL, "null argument");
+    resolve_step_timing(s);
     resolve_shift_timing(s);
     for (int i = 0; i < K_COUNT; ++i) {
         out_calls[i] = s->calls[i];
