@@ -231,6 +231,15 @@ class SimManager:
                       "mbots_pack_observations")
         return out
 
+    def species_blocks(self):
+        """[(start, end)] * 4: the row range of every species in the current exports (rows are species-major,
+        src/sim/sim.cpp:1148-1149). Exact, unlike the cumulative sum of `species_count_tensor` the reference's loop
+        uses (learn/training_loop.py:43-45): those counts are taken before the step's respawns (sim.cpp:804-836)."""
+        A = self.num_agents()
+        base = self.export("DEBUG_ROW_BASE").to_torch()[0].tolist()      # first row of (world 0, species k)
+        starts = [int(b) for b in base] + [A]
+        return [(starts[k], starts[k + 1]) for k in range(4)]
+
     def sample_actions(self, start, end, weights, seed, draw, want_index=False):
         """Categorical sample of rows [start, end) from (n, 6) float32 action weights + one-hot write into
         the action export (training_loop.py:57,77-83,136). Returns the picked indices when asked to."""

@@ -301,10 +301,7 @@ class PolicyRunner:
 
     def species_blocks(self):
         """[(start, end)] * 4 of the current row set: rows are species-major (src/sim/sim.cpp:1148-1149)."""
-        A = self.sim.num_agents()
-        base = self.sim.export("DEBUG_ROW_BASE").to_torch()[0].tolist()     # first row of (world 0, species k)
-        starts = [int(b) for b in base] + [A]
-        return [(starts[k], starts[k + 1]) for k in range(4)]
+        return self.sim.species_blocks()
 
     def act(self, want_index=False):
         import torch

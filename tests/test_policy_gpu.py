@@ -249,3 +249,25 @@ def test_fused_policy_in_the_loop_matches_oracle(cuda_device, layout):
         o.step(); g.step()
         compare(o, g, f"fused policy step {t}")
         o.shift_observations(); g.shift_observations()
+
+
+def test_train_epoch_on_the_gpu_simulator(cuda_device):
+    """the reference's loop body (learn/training_loop.py:36-136) runs end to end on the CUDA
+    SimManager with the memory-input network the loop expects."""
+    import torch
+    from madrona_bots import SimManager
+    from madrona_bots.learn import MemoryA2C, train_epoch
+    torch.manual_seed(2)
+    sim = SimManager(0, 64, 5, 32)
+    nets = [MemoryA2C(rtype=t).to("cuda:0") for t in ("GRU", "LSTM", "RNN", "GRU")]
+    opts = [torch.optim.Adam(n.parameters(), lr=1e-3) for n in nets]
+    g = torch.Generator(device="cuda:0").manual_seed(3)
+    for epoch in range(3):
+        res = train_epoch(sim, nets, opts, generator=g)
+        A = sim.num_agents()
+        assert sum(r[2] for r in res) == A and all(np.isfinite(r[0]) and np.isfinite(r[1]) for r in res)
+        act = sim.action_tensor(False).to_torch()
+        assert act.shape == (A, 6) and bool((act.sum(dim=1) == 1).all())
+        mem = sim.hidden_state_tensor(False).to_torch()
+        assert float(mem.abs().max()) <= 1.0 and float(mem.abs().max()) > 0.0
+        assert torch.equal(sim.position_tensor(True).to_torch(), sim.position_tensor(False).to_torch())
