@@ -379,15 +379,17 @@ const char *launch_policy_fused(const ObsSet &o, uint32_t row_begin, uint32_t ro
     FusedPlan plan;
     const char *err = policy_plan(prog, blob_bytes, plan);
     if (err || rows == 0) return err;
-    static bool attr_set = false;
     const size_t smem = policy_fused_smem_bytes();
-    if (!attr_set) {
-        cudaFuncSetAttribute(policy_fused_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-        attr_set = true;
+    int dev = 0, sms = 148;
+    cudaGetDevice(&dev);
+    static bool attr_set[64] = {};                      /* the opt-in is per device */
+    if (dev >= 0 && dev < 64 && !attr_set[dev]) {
+        if (cudaFuncSetAttribute(policy_fused_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess)
+            return "cudaFuncSetAttribute(MaxDynamicSharedMemorySize) failed";
+        attr_set[dev] = true;
     }
     const uint32_t tiles = (rows + kTileRows - 1) / kTileRows;
-    int dev = 0, sms = 148;
-    if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
     const uint32_t grid = tiles < (uint32_t)sms ? tiles : (uint32_t)sms;      /* persistent: one CTA per SM */
     const ObsPtrs ptrs = {o.depth, o.health, o.position, o.semantic, o.surrounding};
     policy_fused_kernel<<<grid, kFusedThreads, smem, s>>>(ptrs, o.action, row_begin, rows,

@@ -538,14 +538,16 @@ const char *launch_policy_umma(const ObsSet &o, uint32_t row_begin, uint32_t row
     const char *err = policy_umma_plan(prog, blob_bytes, plan);
     if (err || rows == 0) return err;
     if (reinterpret_cast<uintptr_t>(blob) & 15u) return "the blob must be 16-byte aligned";
-    static bool attr_set = false;
-    if (!attr_set) {
-        cudaFuncSetAttribute(policy_umma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kUSmemBytes);
-        attr_set = true;
+    int dev = 0, sms = 148;
+    cudaGetDevice(&dev);
+    static bool attr_set[64] = {};                      /* the opt-in is per device */
+    if (dev >= 0 && dev < 64 && !attr_set[dev]) {
+        if (cudaFuncSetAttribute(policy_umma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kUSmemBytes) != cudaSuccess)
+            return "cudaFuncSetAttribute(MaxDynamicSharedMemorySize) failed";
+        attr_set[dev] = true;
     }
     const uint32_t pairs = ((rows + kUTile - 1) / kUTile + 1) / 2;
-    int dev = 0, sms = 148;
-    if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
     const uint32_t grid = pairs < (uint32_t)sms ? pairs : (uint32_t)sms;      /* persistent: one CTA per SM */
     const UObsPtrs ptrs = {o.depth, o.health, o.position, o.semantic, o.surrounding};
     policy_umma_kernel<<<grid, kUThreads, kUSmemBytes, s>>>(ptrs, o.action, row_begin, rows, static_cast<const unsigned char *>(blob),
