@@ -341,8 +341,9 @@ def run_ours(args, rank, world, local_rank):
     # which waits for the drain). The caller of step t + 1 finds the observations of step t on the host.
     host_out = [{n: torch.empty(rows_cap * b, dtype=torch.uint8).pin_memory() for n, b in obs_names} for _ in range(2)]
     host_sc = [torch.empty(W * 16, dtype=torch.uint8).pin_memory() for _ in range(2)]
-    copy_stream = torch.cuda.Stream(device=dev)
-    drained = [None, None]                            # event: the drain that read row set (step % 2) is complete
+    n_copy = max(1, int(os.environ.get("MBOTS_E2E_COPY_STREAMS", "1")))
+    copy_streams = [torch.cuda.Stream(device=dev) for _ in range(n_copy)]
+    drained = [None, None]                            # events: the drain that read row set (step % 2) is complete
     h2d = d2h = 0
 
     def e2e_step(i):
@@ -352,22 +353,28 @@ def run_ours(args, rank, world, local_rank):
         sim.copy_from_host("ACTION", host_pool[i % POOL].data_ptr(), A * 24)
         h2d += A * 24
         if drained[i % 2] is not None:
-            main.wait_event(drained[i % 2])           # this step's export overwrites the row set drained two steps ago
+            for ev in drained[i % 2]:
+                main.wait_event(ev)                   # this step's export overwrites the row set drained two steps ago
         sim.step()
         sim.shift_observations_async()
         done = torch.cuda.Event()
         done.record(main)
         A = sim.num_agents()
         if drained[(i + 1) % 2] is not None:
-            drained[(i + 1) % 2].synchronize()        # the caller reads the observations of the previous step on the host
-        copy_stream.wait_event(done)
-        for n, b in obs_names:
-            sim.copy_to_host(n, host_out[i % 2][n].data_ptr(), A * b, stream=copy_stream)
+            for ev in drained[(i + 1) % 2]:
+                ev.synchronize()                      # the caller reads the observations of the previous step on the host
+        for cs in copy_streams:
+            cs.wait_event(done)
+        for k, (n, b) in enumerate(obs_names):
+            sim.copy_to_host(n, host_out[i % 2][n].data_ptr(), A * b, stream=copy_streams[k % n_copy])
             d2h += A * b
-        sim.copy_to_host("SPECIES_COUNT", host_sc[i % 2].data_ptr(), W * 16, stream=copy_stream)
+        sim.copy_to_host("SPECIES_COUNT", host_sc[i % 2].data_ptr(), W * 16, stream=copy_streams[0])
         d2h += W * 16
-        drained[i % 2] = torch.cuda.Event()
-        drained[i % 2].record(copy_stream)
+        drained[i % 2] = []
+        for cs in copy_streams:
+            ev = torch.cuda.Event()
+            ev.record(cs)
+            drained[i % 2].append(ev)
 
     for i in range(min(args.warmup, 3)):
         e2e_step(i)
@@ -377,7 +384,8 @@ def run_ours(args, rank, world, local_rank):
     e0.record()
     for i in range(args.steps):
         e2e_step(min(args.warmup, 3) + i)
-    torch.cuda.current_stream().wait_stream(copy_stream)      # the last drain is inside the timed region
+    for cs in copy_streams:
+        torch.cuda.current_stream().wait_stream(cs)           # the last drain is inside the timed region
     e1.record()
     barrier()
     ms_e = allreduce_max(e0.elapsed_time(e1), device=dev)
