@@ -261,3 +261,27 @@ def test_reference_plumbing_single_world_1000_steps(cuda_device):
             compare(o, g, f"epoch {epoch}")
     st = o.episode_stats()
     assert st[1] == 1000 and st[11] > 0 and st[12] > 0
+
+
+def test_async_step_shift_then_sync_matches_oracle(cuda_device):
+    """step_async + shift_observations_async + sync (mbots_sync waits for the step only, the shift keeps running
+    behind it) gives the same rows as the blocking calls, with and without kernel timing enabled."""
+    import torch
+    from oracle_binding import random_actions
+    o, g = make_pair(96, 21, 32)
+    rng = np.random.default_rng(5)
+    for t in range(40):
+        g.profile(t % 2 == 0)
+        A = o.num_agents()
+        assert g.num_agents() == A
+        acts = random_actions(rng, A, "onehot")
+        o.tensor("ACTION")[:] = acts
+        g.action_tensor(False).to_torch().copy_(torch.from_numpy(acts))
+        o.step(); o.shift_observations()
+        g.step_async(); g.shift_observations_async(); g.sync()
+        torch.cuda.synchronize()
+        compare(o, g, f"async step {t}")
+    g.profile(True)
+    g.step_async(); g.shift_observations_async(); g.sync()
+    ms = g.profile_read()
+    assert all(v["calls"] >= 1 for k, v in ms.items() if k in ("step", "export_sense")), ms
