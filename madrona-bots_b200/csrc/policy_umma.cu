@@ -88,14 +88,6 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity)
         asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}"
                      : "=r"(done) : "r"(bar), "r"(parity) : "memory");
 }
-/* busy poll (no suspend window): for the issue warp, whose reaction time is on every tile's critical path */
-__device__ __forceinline__ void mbar_spin(uint32_t bar, uint32_t parity)
-{
-    uint32_t done = 0;
-    while (!done)
-        asm volatile("{\n\t.reg .pred p;\n\tmbarrier.test_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}"
-                     : "=r"(done) : "r"(bar), "r"(parity) : "memory");
-}
 __device__ __forceinline__ void bulk_copy_g2s(uint32_t dst, const void *src, uint32_t bytes, uint32_t bar)
 {
     asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
@@ -468,7 +460,7 @@ policy_umma_kernel(UObsPtrs o, int32_t *__restrict__ action, uint32_t row_begin,
                 if (lane == 0) { UTRACE(10, 0, b) }
 #pragma unroll
                 for (int t = 0; t < 2; ++t) {
-                    mbar_spin(A_READY(t), a_phase);
+                    mbar_wait(A_READY(t), a_phase);     /* suspending wait: a busy poll here takes issue slots from four epilogue warps */
                     if (lane == 0) { UTRACE(11, t, b) }
                     tc_fence_after();
                     const uint64_t adesc = umma_desc(a_base + (uint32_t)t * kUBlockBytes);
