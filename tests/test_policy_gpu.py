@@ -251,6 +251,44 @@ def test_fused_policy_in_the_loop_matches_oracle(cuda_device, layout):
         o.shift_observations(); g.shift_observations()
 
 
+@pytest.mark.parametrize("layout", ["sw128", "rowpad"])
+def test_fused_policy_many_tiles_per_cta(cuda_device, layout):
+    """~200 K rows in one call: every persistent CTA walks several tile pairs, so the weight ring, the barrier
+    phases and the accumulator hand-over wrap around many times (the small cases above stay within one pass)."""
+    import torch
+    from madrona_bots import SimManager
+    from madrona_bots.policy import FusedPolicy, SpeciesPolicy
+    from prims_binding import shim
+    torch.manual_seed(3)
+    net, config = _make("GRU", ["Tanh", "ReLU"])
+    with torch.no_grad():
+        for p in net.parameters():
+            p.mul_(2.0)
+    pol = SpeciesPolicy(config, net.state_dict(), "cuda:0")
+    fused = FusedPolicy(pol, layout)
+    sim = SimManager(0, 6144, 9, 32)
+    _random_steps(sim, 3, 4)
+    A = sim.num_agents()
+    assert A > 148 * 256 * 4
+    idx, lg = sim.policy_act(0, A, fused, seed=2, draw=3, want_index=True, want_logits=True)
+    ref = _bf16_reference_logits(pol, sim.pack_observations(0, A))
+    scale = float(ref.abs().max())
+    err = (lg - ref).abs()
+    assert float(err.max()) <= 3e-2 * scale + 1e-3, (float(err.max()), scale, int(err.argmax()) // 6)
+    assert float(err.mean()) <= 3e-3 * scale + 1e-4
+    l = lg.cpu().numpy().astype(np.float32)
+    w = np.exp((l - l.max(axis=1, keepdims=True)).astype(np.float32)).astype(np.float32)
+    got = idx.cpu().numpy()
+    for lo, hi in ((0, 20000), (A - 20000, A)):               # the host restatement is a Python loop: two slices
+        want = _host_sample(shim(), w[lo:hi], 2, 3, lo)
+        assert int((got[lo:hi] != want).sum()) <= (hi - lo) // 500
+    act = sim.action_tensor(False).to_torch()
+    assert torch.equal(act, torch.nn.functional.one_hot(idx.long(), 6).to(torch.int32))
+    # deterministic: the same call again gives the same picks and logits
+    idx2, lg2 = sim.policy_act(0, A, fused, seed=2, draw=3, want_index=True, want_logits=True)
+    assert torch.equal(idx, idx2) and torch.equal(lg, lg2)
+
+
 def test_train_epoch_on_the_gpu_simulator(cuda_device):
     """the reference's loop body (learn/training_loop.py:36-136) runs end to end on the CUDA
     SimManager with the memory-input network the loop expects."""
