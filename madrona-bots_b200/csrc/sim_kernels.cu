@@ -934,38 +934,70 @@ export_kernel(SimDev d, int cur, int with_sensors, uint32_t slots, uint32_t tile
 /* ------------------------------------------------------------------------- */
 /* shift_kernel: cur -> prev for every row below totalAgents                   */
 
-__global__ void __launch_bounds__(256) shift_kernel(SimDev d, int cur)
+#ifndef MBK_SHIFT_BATCH
+#define MBK_SHIFT_BATCH 4
+#endif
+#ifndef MBK_SHIFT_CS
+#define MBK_SHIFT_CS 0
+#endif
+template <typename V> __device__ __forceinline__ V shift_ld(const V *p)
+{
+#if MBK_SHIFT_CS
+    return __ldcs(p);
+#else
+    return *p;
+#endif
+}
+template <typename V> __device__ __forceinline__ void shift_st(V *p, V v)
+{
+#if MBK_SHIFT_CS
+    __stcs(p, v);
+#else
+    *p = v;
+#endif
+}
+/* Plain column copy with MBK_SHIFT_BATCH independent loads in flight per thread before the first store (the
+ * columns never alias; without the batching every store waits on its own load and an SM keeps only ~32 KB in
+ * flight). The last, partial batch is predicated, not serialised. */
+template <typename V, typename F>
+__device__ __forceinline__ void shift_column(V *__restrict__ p, const V *__restrict__ s, size_t n, size_t t0,
+                                             size_t stride, F fix)
+{
+    for (size_t i = t0; i < n; i += MBK_SHIFT_BATCH * stride) {
+        V v[MBK_SHIFT_BATCH];
+#pragma unroll
+        for (int u = 0; u < MBK_SHIFT_BATCH; ++u)
+            if (i + u * stride < n) v[u] = shift_ld(s + i + u * stride);
+#pragma unroll
+        for (int u = 0; u < MBK_SHIFT_BATCH; ++u)
+            if (i + u * stride < n) shift_st(p + i + u * stride, fix(v[u]));
+    }
+}
+
+#ifndef MBK_SHIFT_MIN_BLOCKS
+#define MBK_SHIFT_MIN_BLOCKS 4
+#endif
+#ifndef MBK_SHIFT_CTAS_PER_SM
+#define MBK_SHIFT_CTAS_PER_SM 4
+#endif
+__global__ void __launch_bounds__(256, MBK_SHIFT_MIN_BLOCKS) shift_kernel(SimDev d, int cur)
 {
     const ObsSet &o = d.obs[cur];
     const size_t A = d.totals->totalAgents;
     const size_t stride = (size_t)gridDim.x * blockDim.x;
     const size_t t0 = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    auto same = [](auto v) { return v; };
     /* hidden: 4 x 16 B per row */
-    {
-        const float4 *s = reinterpret_cast<const float4 *>(o.hidden);
-        float4 *p = reinterpret_cast<float4 *>(o.prev_hidden);
-        for (size_t i = t0; i < A * 4; i += stride) p[i] = s[i];
-    }
-    /* action: 24 B per row = 3 x 8 B; 2 rows = 3 x 16 B */
-    {
-        const int2 *s = reinterpret_cast<const int2 *>(o.action);
-        int2 *p = reinterpret_cast<int2 *>(o.prev_action);
-        for (size_t i = t0; i < A * 3; i += stride) p[i] = s[i];
-    }
+    shift_column(reinterpret_cast<float4 *>(o.prev_hidden), reinterpret_cast<const float4 *>(o.hidden), A * 4, t0, stride, same);
+    /* action: 24 B per row = 3 x 8 B */
+    shift_column(reinterpret_cast<int2 *>(o.prev_action), reinterpret_cast<const int2 *>(o.action), A * 3, t0, stride, same);
     /* stats, with the reference's field mix-up (src/sim/sim.cpp:1034, U7) */
-    {
-        const int4 *s = reinterpret_cast<const int4 *>(o.stats);
-        int4 *p = reinterpret_cast<int4 *>(o.prev_stats);
-        for (size_t i = t0; i < A; i += stride) { const int4 v = s[i]; p[i] = make_int4(v.x, v.x, v.z, v.w); }
-    }
-    {
-        const float2 *s = reinterpret_cast<const float2 *>(o.position);
-        float2 *p = reinterpret_cast<float2 *>(o.prev_position);
-        const float2 *s2 = reinterpret_cast<const float2 *>(o.surrounding);
-        float2 *p2 = reinterpret_cast<float2 *>(o.prev_surrounding);
-        for (size_t i = t0; i < A; i += stride) { p[i] = s[i]; p2[i] = s2[i]; }
-    }
-    for (size_t i = t0; i < A; i += stride) { o.prev_health[i] = o.health[i]; o.prev_reward[i] = o.reward[i]; }
+    shift_column(reinterpret_cast<int4 *>(o.prev_stats), reinterpret_cast<const int4 *>(o.stats), A, t0, stride,
+                 [](int4 v) { return make_int4(v.x, v.x, v.z, v.w); });
+    shift_column(reinterpret_cast<float2 *>(o.prev_position), reinterpret_cast<const float2 *>(o.position), A, t0, stride, same);
+    shift_column(reinterpret_cast<float2 *>(o.prev_surrounding), reinterpret_cast<const float2 *>(o.surrounding), A, t0, stride, same);
+    shift_column(o.prev_health, o.health, A, t0, stride, same);
+    shift_column(o.prev_reward, o.reward, A, t0, stride, same);
 }
 
 /* ------------------------------------------------------------------------- */
@@ -1076,7 +1108,7 @@ void launch_shift(const SimDev &d, int cur, uint32_t rows_upper, cudaStream_t s)
     /* enough CTAs to cover the hidden-state column at one 16-B vector per thread, capped */
     size_t vecs = (size_t)rows_upper * 4;
     size_t blocks = (vecs + 255) / 256;
-    if (blocks > 148 * 16) blocks = 148 * 16;
+    if (blocks > 148 * MBK_SHIFT_CTAS_PER_SM) blocks = 148 * MBK_SHIFT_CTAS_PER_SM;
     if (blocks == 0) blocks = 1;
     shift_kernel<<<(unsigned)blocks, 256, 0, s>>>(d, cur);
 }

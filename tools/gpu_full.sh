@@ -1,9 +1,9 @@
 #!/bin/bash
-# one GPU-box pass: parity tests, bench, ncu launch list, ncu --set full of the two main kernels
+# one GPU-box pass: parity tests, bench, ncu launch list, ncu --set full of step, export and shift kernels
 TAG=${1:-r1c}
 mkdir -p gpurun_out
 timeout 600 python -m pytest tests -m gpu -x -q > gpurun_out/${TAG}_tests.log 2>&1; tail -3 gpurun_out/${TAG}_tests.log
 timeout 400 python bench.py > gpurun_out/${TAG}_bench.json 2> gpurun_out/${TAG}_bench.err; tail -2 gpurun_out/${TAG}_bench.err; cat gpurun_out/${TAG}_bench.json
 timeout 300 ncu --metrics gpu__time_duration.sum --clock-control none -c 200 --csv --log-file gpurun_out/${TAG}_launches.csv python bench.py --steps 5 --warmup 3 --no-cpu-baseline > gpurun_out/${TAG}_ncu1.log 2>&1
-timeout 600 ncu --set full --clock-control none --import-source on -k regex:"export_kernel|step_kernel" -s 12 -c 3 -o gpurun_out/${TAG}_full -f python bench.py --steps 5 --warmup 3 --no-cpu-baseline > gpurun_out/${TAG}_ncu2.log 2>&1
+timeout 600 ncu --set full --clock-control none --import-source on -k regex:"export_kernel|step_kernel|shift_kernel" -s 16 -c 4 -o gpurun_out/${TAG}_full -f python bench.py --steps 5 --warmup 3 --no-cpu-baseline > gpurun_out/${TAG}_ncu2.log 2>&1
 ls -la gpurun_out
