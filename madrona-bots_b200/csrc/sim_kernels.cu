@@ -82,7 +82,10 @@ __global__ void init_kernel(SimDev d)
 /* warp's shared memory, cross-agent effects are shared-memory atomics, and    */
 /* every count / rank is a ballot + popc or a warp reduction.                  */
 
-constexpr int kStepWarps = 4;
+#ifndef MBK_STEP_WARPS
+#define MBK_STEP_WARPS 4
+#endif
+constexpr int kStepWarps = MBK_STEP_WARPS;           /* worlds (warps) per CTA */
 
 /* per-warp shared memory, sized for `slots` >= the largest world before the step */
 struct StepLayout { uint32_t chunkAgents, chunkSpeed, food, pose, accum, oldrow, info, spec, total; };
@@ -125,7 +128,7 @@ __device__ __forceinline__ uint32_t food_match(const uint2 &f, uint32_t cell)
 __device__ __forceinline__ int warp_sum(int v) { return __reduce_add_sync(FULL, v); }
 
 #ifndef MBK_STEP_MIN_BLOCKS
-#define MBK_STEP_MIN_BLOCKS 8
+#define MBK_STEP_MIN_BLOCKS (32 / MBK_STEP_WARPS)
 #endif
 __global__ void __launch_bounds__(kStepWarps * 32, MBK_STEP_MIN_BLOCKS) step_kernel(SimDev d, int cur, uint32_t slots)
 {
@@ -554,7 +557,11 @@ __global__ void __launch_bounds__(kScanTile) scan_kernel(SimDev d, int cur, int 
 /*         tile. Launched after the FAST kernel for the worlds it skipped, and  */
 /*         alone when the host has no fresh bound on the population.            */
 
-constexpr int kExportWarps = 4;
+#ifndef MBK_EXPORT_WARPS
+#define MBK_EXPORT_WARPS 1
+#endif
+constexpr int kExportWarps = MBK_EXPORT_WARPS;      /* worlds (warps) per CTA */
+constexpr int kExportFastMinBlocks = 28 / kExportWarps;   /* 28 warps per SM at <= 72 registers */
 constexpr int kQueue = 64;           /* pending pairs / pending exact tests of a warp: < 32 carried over, + <= 32 pushed */
 constexpr int kFastSlots = 64;       /* 6 slot bits in a 32-bit key */
 constexpr int kFullTile = 8;
@@ -908,15 +915,15 @@ __device__ __forceinline__ void export_world(const SimDev &d, int cur, int with_
  *       full -> worlds with at most `skip_upto` agents were done by the FAST kernel (grid-stride over the
  *               worlds with a small grid, and nothing at all when no world is that large). */
 template <bool FAST>
-__global__ void __launch_bounds__(kExportWarps * 32, FAST ? 7 : 4)
+__global__ void __launch_bounds__(kExportWarps * 32, FAST ? kExportFastMinBlocks : 16 / kExportWarps)
 export_kernel(SimDev d, int cur, int with_sensors, uint32_t slots, uint32_t tile, int skip_upto)
 {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     const int warp = threadIdx.x >> 5;
     if (!FAST && skip_upto >= 0 && (int)d.totals->maxWorldCount <= skip_upto) return;
     unsigned char *my = smem_raw + (size_t)export_layout(slots, tile, sizeof(typename Sense<FAST>::Key)).total * warp;
-    if (FAST) {                                     /* one world per warp */
-        const uint32_t w = blockIdx.x * kExportWarps + warp;
+    if (FAST) {
+        const uint32_t w = blockIdx.x * kExportWarps + warp;    /* one world per warp */
         if (w >= d.numWorlds) return;               /* whole warp: no block-level barrier anywhere */
         const int n = d.worldCount[w];
         if (n > (int)slots || n > 63) return;       /* slot 63 is the miss sentinel of the 32-bit keys */
