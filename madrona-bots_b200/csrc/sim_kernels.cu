@@ -561,7 +561,13 @@ __global__ void __launch_bounds__(kScanTile) scan_kernel(SimDev d, int cur, int 
 #define MBK_EXPORT_WARPS 1
 #endif
 constexpr int kExportWarps = MBK_EXPORT_WARPS;      /* worlds (warps) per CTA */
-constexpr int kExportFastMinBlocks = 28 / kExportWarps;   /* 28 warps per SM at <= 72 registers */
+#ifndef MBK_EXPORT_SM_WARPS
+#define MBK_EXPORT_SM_WARPS 28                       /* resident warps per SM the FAST kernel is built for (<= 72 registers) */
+#endif
+#ifndef MBK_EXPORT_TILE_MIN
+#define MBK_EXPORT_TILE_MIN 40
+#endif
+constexpr int kExportFastMinBlocks = MBK_EXPORT_SM_WARPS / kExportWarps;
 constexpr int kQueue = 64;           /* pending pairs / pending exact tests of a warp: < 32 carried over, + <= 32 pushed */
 constexpr int kFastSlots = 64;       /* 6 slot bits in a 32-bit key */
 constexpr int kFullTile = 8;
@@ -599,7 +605,9 @@ __host__ __device__ inline ExportLayout export_layout(uint32_t slots, uint32_t t
     L.pairq = o; o += kQueue * 4;
     L.candq = o; o += kQueue * 4;
     L.newrow = o; o += slots * 4;
-    L.oldrow = o; o += slots * 4;
+    /* old rows are dead once the columns are carried, the queues idle until then: share the bytes when they fit
+     * (FAST: 28 single-warp CTAs of 56 slots then fit one SM's shared memory, not 26) */
+    if (slots <= (uint32_t)kQueue) L.oldrow = L.queue; else { L.oldrow = o; o += slots * 4; }
     L.theta = o; o += slots * 4;
     L.spec = o; o += slots < 64u ? 64u : (slots + 15u) & ~15u;   /* FAST reads the 0xff sentinel at [63] */
     L.total = (o + 15u) & ~15u;
@@ -1103,7 +1111,8 @@ int launch_export(const SimDev &d, int cur, int with_sensors, uint32_t bound, cu
     }
     /* one tile = the whole world for all but the largest worlds */
     uint32_t tile = d.initAgents + 8u;
-    if (tile < 40u) tile = 40u;
+    if (tile < (uint32_t)MBK_EXPORT_TILE_MIN) tile = (uint32_t)MBK_EXPORT_TILE_MIN;
+    if (MBK_EXPORT_TILE_MIN < 40) tile = (uint32_t)MBK_EXPORT_TILE_MIN;   /* experiment: smaller sensor tiles */
     if (tile > fast_slots) tile = fast_slots;
     launch_export_variant<true>(d, cur, with_sensors, fast_slots, tile, 0, s);
     launch_export_variant<false>(d, cur, with_sensors, d.cap, kFullTile, (int)(fast_slots < 63u ? fast_slots : 63u), s);
