@@ -48,10 +48,10 @@ ALGO_BYTES = {"step": 24 + 28 + 24 + 9.0, "export_sense": 44 + 64 + 64 + 64, "sh
 # bytes the export kernel really has to move per agent given that rows move every step:
 MOVED_BYTES_EXPORT = 280 + 280 + 36 + 64 + 4 + 2 + 41
 # dram__bytes_read.sum + dram__bytes_write.sum of export_kernel<FAST> per agent, from the committed
-# `ncu --set full` capture (profiles/r1d_ncu_full_summary.txt: 705.4 MB + 809.1 MB at 2,173,116 agents)
-NCU_TRAFFIC_BYTES_PER_AGENT_EXPORT = (705.409024e6 + 809.079040e6) / 2173116.0
-# same capture (profiles/r1e_ncu_full_summary.txt): what actually bounds the kernel is instruction issue
-NCU_EXPORT_ISSUE = {"warp_instructions_per_world": 461542924 / 65536.0, "issue_active_frac": 0.712}
+# `ncu --set full` capture (profiles/r1k_ncu_full_summary.txt: 705.5 MB + 808.9 MB at 2,173,116 agents)
+NCU_TRAFFIC_BYTES_PER_AGENT_EXPORT = (705.549568e6 + 808.883200e6) / 2173116.0
+# same capture: what actually bounds the kernel is instruction issue
+NCU_EXPORT_ISSUE = {"warp_instructions_per_world": 445786274 / 65536.0, "issue_active_frac": 0.765}
 
 
 def measured_peaks():

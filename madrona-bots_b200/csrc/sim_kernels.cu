@@ -543,7 +543,9 @@ __global__ void __launch_bounds__(kScanTile) scan_kernel(SimDev d, int cur, int 
 }
 
 /* ------------------------------------------------------------------------- */
-/* export_kernel: one WARP per world, kExportWarps independent worlds per CTA.  */
+/* export_kernel: one WARP per world, kExportWarps independent worlds per CTA    */
+/* (one: worlds differ in population, and a CTA of four held its slot until    */
+/* the slowest world was done -- 10 % of the warp slots idled).                */
 /* No block barriers: every phase of a world is synchronised with __syncwarp,   */
 /* so warps drift apart and hide each other's memory latency.                   */
 /*                                                                             */
@@ -551,8 +553,8 @@ __global__ void __launch_bounds__(kScanTile) scan_kernel(SimDev d, int cur, int 
 /*   FAST  worlds of at most `slots` <= 64 agents (every world of a normal     */
 /*         rollout). Nearest hits are 32-bit keys -- (t bits - bits(1.0f)) in   */
 /*         26 bits, target slot in 6 -- so one native shared-memory atomicMin   */
-/*         keeps them, and the keys of `tile` <= 64 observers fit beside the    */
-/*         agent arrays: a whole world is one sensor tile.                      */
+/*         keeps them, and the keys of a tile of 32 observers (4 KB) fit beside */
+/*         the agent arrays with 32 such CTAs resident per SM.                  */
 /*   full  any world up to the capacity (<= 1024): 64-bit keys, 8 observers per */
 /*         tile. Launched after the FAST kernel for the worlds it skipped, and  */
 /*         alone when the host has no fresh bound on the population.            */
@@ -562,10 +564,10 @@ __global__ void __launch_bounds__(kScanTile) scan_kernel(SimDev d, int cur, int 
 #endif
 constexpr int kExportWarps = MBK_EXPORT_WARPS;      /* worlds (warps) per CTA */
 #ifndef MBK_EXPORT_SM_WARPS
-#define MBK_EXPORT_SM_WARPS 28                       /* resident warps per SM the FAST kernel is built for (<= 72 registers) */
+#define MBK_EXPORT_SM_WARPS 32                       /* resident warps per SM the FAST kernel is built for (<= 64 registers) */
 #endif
-#ifndef MBK_EXPORT_TILE_MIN
-#define MBK_EXPORT_TILE_MIN 40
+#ifndef MBK_EXPORT_FAST_TILE
+#define MBK_EXPORT_FAST_TILE 32                      /* observers per sensor tile of the FAST kernel: 4 KB of keys */
 #endif
 constexpr int kExportFastMinBlocks = MBK_EXPORT_SM_WARPS / kExportWarps;
 constexpr int kQueue = 64;           /* pending pairs / pending exact tests of a warp: < 32 carried over, + <= 32 pushed */
@@ -1109,10 +1111,9 @@ int launch_export(const SimDev &d, int cur, int with_sensors, uint32_t bound, cu
         launch_export_variant<false>(d, cur, with_sensors, d.cap, kFullTile, -1, s);
         return 1;
     }
-    /* one tile = the whole world for all but the largest worlds */
-    uint32_t tile = d.initAgents + 8u;
-    if (tile < (uint32_t)MBK_EXPORT_TILE_MIN) tile = (uint32_t)MBK_EXPORT_TILE_MIN;
-    if (MBK_EXPORT_TILE_MIN < 40) tile = (uint32_t)MBK_EXPORT_TILE_MIN;   /* experiment: smaller sensor tiles */
+    /* 32 observers per sensor tile: 56 slots + 4 KB of keys = 6.1 KB per single-warp CTA, 32 of them per SM.
+     * (One tile for the whole world -- 40 observers, 26-28 CTAs per SM -- measured 1 % slower.) */
+    uint32_t tile = (uint32_t)MBK_EXPORT_FAST_TILE;
     if (tile > fast_slots) tile = fast_slots;
     launch_export_variant<true>(d, cur, with_sensors, fast_slots, tile, 0, s);
     launch_export_variant<false>(d, cur, with_sensors, d.cap, kFullTile, (int)(fast_slots < 63u ? fast_slots : 63u), s);
