@@ -210,7 +210,7 @@ def run_reference(args, rank, world):
     line = {
         "impl": "reference", "metric": METRIC, "value": val, "unit": UNIT, "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * dt / args.steps,
-        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32+i32",
+        "higher_is_better": True, "scaling": args.scaling, "vs_baseline": None, "dtype": "f32+i32",
         "data": "synthetic", "gpu_launches": 0,
         "config": workload_config(args, sample=f"{sample_worlds} of the {args.worlds_per_gpu} worlds per step"),
         "cpu_baseline": {"value": val, "unit": UNIT, "cores": cores, "kind": "port",
@@ -423,7 +423,7 @@ def run_ours(args, rank, world, local_rank):
         kernels[name] = ent
     line = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
-        "ms_per_step": ms_max / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "ms_per_step": ms_max / args.steps, "higher_is_better": True, "scaling": args.scaling, "vs_baseline": None,
         "dtype": "f32+i32", "data": "synthetic",
         "config": dict(workload_config(args), host_affinity=(f"rank bound to its GPU's {bound_cpus} local CPUs (NVML)"
                                                               if bound_cpus else "unchanged")),
@@ -458,13 +458,19 @@ def main():
     ap.add_argument("--steps", type=int, default=50)
     ap.add_argument("--warmup", type=int, default=10)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--worlds-per-gpu", type=int, default=65536)
+    ap.add_argument("--worlds", type=int, default=65536,
+                    help="TOTAL worlds of the job, sharded over the GPUs (BASELINE.json configs[3]: strong scaling)")
+    ap.add_argument("--worlds-per-gpu", type=int, default=0,
+                    help="fixed worlds per GPU instead (weak scaling); 0 = --worlds // --gpus")
     ap.add_argument("--ref-worlds", type=int, default=4096, help="worlds per step of the CPU reference arm")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--cap", type=int, default=0, help="per-world slot capacity (0 = library default, 128)")
     args = ap.parse_args()
     if args.warmup < 3:
         args.warmup = 3
+    args.scaling = "weak" if args.worlds_per_gpu > 0 else "strong"
+    if args.worlds_per_gpu <= 0:
+        args.worlds_per_gpu = max(1, args.worlds // max(1, args.gpus))
 
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))

@@ -157,7 +157,7 @@ __global__ void __launch_bounds__(kStepWarps * 32, MBK_STEP_MIN_BLOCKS) step_ker
      * before the live count is known -- slots below the capacity always exist), the per-world scalars and the
      * food records; (2) the action rows, whose addresses come from (1). Larger worlds take further passes. */
     const bool has_b = 32u + (uint32_t)lane < cap;
-    const size_t ia = base + lane, ib = base + 32 + (has_b ? lane : 0);
+    const size_t ia = base + lane, ib = has_b ? base + 32 + lane : ia;   /* never form an address outside the world's slots */
     float4 pose_a = d.pose[ia], pose_b = d.pose[ib];
     int hp_a = d.health[ia], hp_b = d.health[ib];
     uint32_t sp_a = d.species[ia], sp_b = d.species[ib];
@@ -875,6 +875,7 @@ __device__ __forceinline__ void export_world(const SimDev &d, int cur, int with_
         __syncwarp();
         spans(lane < cqn ? candq[lane] : 0u, lane < cqn);
         expand(lane < pqn ? pairq[lane] : 0u, lane < pqn, true);
+        __syncwarp();                                   /* the decode below reads keys other lanes wrote with atomicMin */
 
         for (int idx = lane; idx < m * 8; idx += 32) {
             const int ol = idx >> 3, quad = idx & 7, i = tile0 + ol;

@@ -30,6 +30,34 @@ def test_rollout_1024_worlds(cuda_device):
     drive(o, g, steps=60, seed=1234, mode="onehot", check_every=10)
 
 
+def test_rollout_1024_worlds_1000_steps(cuda_device):
+    """BASELINE.json configs[1] / SURVEY.md section 7 as written: 1,024 worlds for 1,000 random-action steps,
+    every export compared with the oracle every 50 steps (and after the last)."""
+    o, g = make_pair(1024, 0, 32)
+    drive(o, g, steps=1000, seed=4321, mode="onehot", check_every=50, write_hidden=False)
+    st = o.episode_stats()
+    assert st[1] == 1000 and st[10] > 0 and st[11] > 0 and st[12] > 0, st
+
+
+def test_rollout_2500_worlds_partial_scan_tile(cuda_device):
+    """Three tiles of the row scan (1,024 worlds each), the last one partial: the cross-tile prefix of the
+    species-major row assignment (the reference's global sort, src/sim/sim.cpp:1148-1149) against the oracle."""
+    o, g = make_pair(2500, 17, 32)
+    drive(o, g, steps=40, seed=99, mode="bits", check_every=5)
+
+
+def test_rollout_16384_worlds(cuda_device):
+    """BASELINE.json configs[2]: 16,384 worlds on one GPU, 20 steps, every export against the oracle."""
+    o, g = make_pair(16384, 0, 32)
+    drive(o, g, steps=20, seed=77, mode="onehot", check_every=5)
+
+
+def test_rollout_65536_worlds(cuda_device):
+    """The headline size (65,536 worlds on one GPU), 5 steps, every export against the oracle."""
+    o, g = make_pair(65536, 0, 32)
+    drive(o, g, steps=5, seed=55, mode="onehot", check_every=5, write_hidden=False)
+
+
 def test_capacity_overflow(cuda_device):
     """Slot table full: births and respawns beyond the capacity are dropped and counted (D1)."""
     o, g = make_pair(32, 3, 32, cap=32)
