@@ -127,6 +127,23 @@ int mbots_step_async(mbots_sim *sim, void *stream);
  * sync lets the shift run while the host prepares the next step. */
 int mbots_sync(mbots_sim *sim, void *stream);
 
+/* One rollout step as ONE launch (a cached CUDA graph; the reference launches one graph per step too,
+ * M/src/mw/cuda_exec.cpp:2977-2981): [write the action rows] -> step + sensor -> [shift observations].
+ *   actions_dev  device pointer to (action_rows, 6) int32 rows in observation-row order, or NULL to leave the
+ *                action export as the caller wrote it through its view. min(live agents, action_rows) rows are
+ *                written; the live count is read ON THE DEVICE, so the host may enqueue steps without knowing it.
+ *   shift        non-zero: Manager::shiftObservations of the new rows follows the step.
+ * Nothing is waited for. Several steps may be in flight (the host runs ahead of the device); launch geometry is
+ * then sized from the newest population that has reached the host plus slack, and worlds that outgrow it take the
+ * slower general-capacity kernels -- never a wrong result. mbots_sync() waits for the last enqueued step.
+ * mbots_step / mbots_step_async use the same graphs (without the action write and the shift). MBOTS_GRAPHS=0 in the
+ * environment falls back to plain stream launches; so does mbots_profile(sim, 1) (events sit between the kernels). */
+int mbots_rollout_step_async(mbots_sim *sim, const int32_t *actions_dev, uint64_t action_rows, int32_t shift, void *stream);
+/* The action write alone (asynchronous, row count resolved on the device as above). */
+int mbots_write_actions(mbots_sim *sim, const int32_t *actions_dev, uint64_t action_rows, void *stream);
+/* Number of step graphs launched by this handle since creation (bench bookkeeping). */
+int mbots_graph_launch_count(mbots_sim *sim, uint64_t *out);
+
 /* Manager::shiftObservations (src/entry/mgr.cpp:194-197). Blocking. */
 int mbots_shift_observations(mbots_sim *sim, void *stream);
 int mbots_shift_observations_async(mbots_sim *sim, void *stream);

@@ -7,9 +7,12 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 #include <stdio.h>
+#include <stdlib.h>
 #include <string.h>
 #include <string>
 #include <vector>
+#include <map>
+#include <tuple>
 #include <new>
 
 #include "../../include/mbots.h"
@@ -33,6 +36,21 @@ static int fail(int code, const char *what, cudaError_t ce = cudaSuccess)
 
 enum { K_STEP = 0, K_SCAN = 1, K_EXPORT = 2, K_SHIFT = 3, K_COUNT = 4 };
 
+/* One step's kernel chain as a CUDA graph (the reference launches one graph per step too,
+ * M/src/mw/cuda_exec.cpp:2977-2981): [action write] -> step -> tile sums -> row scan -> export (fast, full) ->
+ * 40-byte copy of the totals -> event -> [shift]. Everything a launch bakes in is part of the key. */
+struct ChainKey {
+    int cur, withShift;
+    uint32_t stepSlots, bound, rowsUpper;
+    const void *actions;
+    unsigned long long actionRows;
+    bool operator<(const ChainKey &o) const
+    {
+        return std::tie(cur, withShift, stepSlots, bound, rowsUpper, actions, actionRows) <
+               std::tie(o.cur, o.withShift, o.stepSlots, o.bound, o.rowsUpper, o.actions, o.actionRows);
+    }
+};
+
 struct mbots_sim {
     mbots_config cfg;
     SimDev d;
@@ -53,6 +71,11 @@ struct mbots_sim {
     bool stepPending;              /* ev[0..3] recorded, elapsed times not read yet */
     double ms[K_COUNT];
     uint32_t calls[K_COUNT];
+    /* step graphs */
+    bool useGraphs;
+    cudaStream_t capStream;        /* capture happens here: the caller's stream may be the legacy default stream */
+    std::map<ChainKey, cudaGraphExec_t> graphs;
+    uint64_t graphLaunches;
 };
 
 namespace {
@@ -135,6 +158,9 @@ void free_all(mbots_sim *s)
     for (auto &e : s->ev) if (e) cudaEventDestroy(e);
     for (auto &e : s->evShift) if (e) cudaEventDestroy(e);
     if (s->evTotals) cudaEventDestroy(s->evTotals);
+    for (auto &kv : s->graphs) cudaGraphExecDestroy(kv.second);
+    s->graphs.clear();
+    if (s->capStream) cudaStreamDestroy(s->capStream);
 }
 
 /* Kernel timing events are read lazily so that profiling never turns an asynchronous call into a blocking one:
@@ -192,27 +218,107 @@ int enqueue_repack(mbots_sim *s, cudaStream_t st, int with_sensors, int count_st
     return MBOTS_OK;
 }
 
-int enqueue_step(mbots_sim *s, cudaStream_t st)
+uint32_t pow2_at_least(uint32_t v)
 {
-    if (s->profile) { resolve_step_timing(s); cudaEventRecord(s->ev[0], st); }
-    /* block size: the largest world known from the last synchronised step (rounded to a warp), or
-     * the capacity when counts are stale because steps were enqueued without a sync in between */
-    uint32_t threads = s->d.cap, bound = 0;
-    if (!s->dirty) {
-        uint32_t need = s->hTotals->maxWorldCount;
-        if (need < s->d.initAgents) need = s->d.initAgents;
-        if (need < 32u) need = 32u;
-        threads = (need + 31u) & ~31u;
-        /* what the export kernel's fast variant is sized for; a world that outgrows it in this one step
-         * (it could double) is picked up by the full variant */
-        bound = need + 8u;
+    uint32_t p = 256;
+    while (p < v && p < 0x80000000u) p <<= 1;
+    return p;
+}
+
+/* Launch geometry of the next step. With the host in step with the device (no step enqueued since the last sync)
+ * it is sized from the exact totals; while steps are in flight, from the newest totals that have landed in the
+ * pinned mirror plus slack. The bounds only size shared memory, grids and the fast / full split of the export:
+ * a world that outgrows them is still handled (step: capacity-sized when unsure; export: the full variant). */
+ChainKey chain_key(mbots_sim *s, const void *actions, unsigned long long action_rows, int with_shift)
+{
+    ChainKey k;
+    uint32_t need = s->hTotals->maxWorldCount;
+    if (need < s->d.initAgents) need = s->d.initAgents;
+    if (need < 32u) need = 32u;
+    uint32_t rows = s->hTotals->totalAgents;
+    if (s->dirty) {
+        need += 8u;
+        rows += rows / 4u + 1024u;
     }
-    launch_step(s->d, s->cur, threads, st);
-    if (s->profile) cudaEventRecord(s->ev[1], st);
-    s->launches += 1;
-    int rc = enqueue_repack(s, st, 1, 1, bound);
-    if (rc != MBOTS_OK) return rc;
-    if (s->profile) s->stepPending = true;
+    const uint64_t cap_rows = (uint64_t)s->d.numWorlds * s->d.cap;
+    if (rows > cap_rows) rows = (uint32_t)cap_rows;
+    k.cur = s->cur;
+    k.withShift = with_shift;
+    k.stepSlots = s->dirty ? s->d.cap : ((need + 31u) & ~31u);
+    if (k.stepSlots > s->d.cap) k.stepSlots = s->d.cap;
+    k.bound = ((need + 8u) + 7u) & ~7u;                 /* launch_export rounds to 8 anyway */
+    k.rowsUpper = pow2_at_least(rows);
+    k.actions = actions;
+    k.actionRows = actions ? action_rows : 0ull;
+    return k;
+}
+
+/* the chain itself, on `st` (a real stream, or the capture stream). Returns the kernels launched. */
+int record_chain(mbots_sim *s, const ChainKey &k, cudaStream_t st, bool timing, bool external_event, int *launches)
+{
+    int n = 0;
+    if (k.actions) { launch_action_write(s->d, k.cur, k.actions, k.actionRows, k.rowsUpper, st); n += 1; }
+    if (timing) cudaEventRecord(s->ev[0], st);
+    launch_step(s->d, k.cur, k.stepSlots, st);
+    if (timing) cudaEventRecord(s->ev[1], st);
+    launch_scan(s->d, k.cur, 1, st);
+    if (timing) cudaEventRecord(s->ev[2], st);
+    n += 3 + launch_export(s->d, k.cur, 1, k.bound, st);
+    if (timing) cudaEventRecord(s->ev[3], st);
+    CU(cudaGetLastError());
+    CU(cudaMemcpyAsync(s->hTotals, s->d.totals, sizeof(Totals), cudaMemcpyDeviceToHost, st));
+    if (external_event) CU(cudaEventRecordWithFlags(s->evTotals, st, cudaEventRecordExternal));
+    else CU(cudaEventRecord(s->evTotals, st));
+    if (k.withShift) {
+        if (timing) cudaEventRecord(s->evShift[0], st);
+        launch_shift(s->d, k.cur ^ 1, k.rowsUpper, st);
+        if (timing) cudaEventRecord(s->evShift[1], st);
+        n += 1;
+        CU(cudaGetLastError());
+    }
+    *launches = n;
+    return MBOTS_OK;
+}
+
+int chain_launch_count(const ChainKey &k) { return 5 + (k.actions ? 1 : 0) + (k.withShift ? 1 : 0); }
+
+int enqueue_step(mbots_sim *s, cudaStream_t st, const void *actions = nullptr, unsigned long long action_rows = 0,
+                 int with_shift = 0)
+{
+    const ChainKey k = chain_key(s, actions, action_rows, with_shift);
+    int n = 0;
+    if (s->profile || !s->useGraphs) {
+        /* per-kernel timing wants events between the kernels: plain stream launches */
+        if (s->profile) { resolve_step_timing(s); if (with_shift) resolve_shift_timing(s); }
+        int rc = record_chain(s, k, st, s->profile, false, &n);
+        if (rc != MBOTS_OK) return rc;
+        if (s->profile) { s->stepPending = true; if (with_shift) s->shiftPending = true; }
+    } else {
+        auto it = s->graphs.find(k);
+        if (it == s->graphs.end()) {
+            if (s->graphs.size() >= 256) {              /* geometry keeps changing: start over rather than grow */
+                for (auto &kv : s->graphs) cudaGraphExecDestroy(kv.second);
+                s->graphs.clear();
+            }
+            cudaGraph_t g = nullptr;
+            CU(cudaStreamBeginCapture(s->capStream, cudaStreamCaptureModeThreadLocal));
+            int rc = record_chain(s, k, s->capStream, false, true, &n);
+            cudaError_t ce = cudaStreamEndCapture(s->capStream, &g);
+            if (rc != MBOTS_OK) { if (g) cudaGraphDestroy(g); return rc; }
+            if (ce != cudaSuccess) return fail(MBOTS_ECUDA, "cudaStreamEndCapture", ce);
+            cudaGraphExec_t ex = nullptr;
+            ce = cudaGraphInstantiate(&ex, g, 0);
+            cudaGraphDestroy(g);
+            if (ce != cudaSuccess) return fail(MBOTS_ECUDA, "cudaGraphInstantiate", ce);
+            it = s->graphs.emplace(k, ex).first;
+        }
+        CU(cudaGraphLaunch(it->second, st));
+        n = chain_launch_count(k);
+        s->graphLaunches += 1;
+    }
+    s->cur ^= 1;
+    s->launches += (uint64_t)n;
+    s->dirty = true;
     return MBOTS_OK;
 }
 
@@ -260,10 +366,12 @@ int mbots_create_ex(const mbots_config *cfg, mbots_sim **out)
         for (auto &ev : s->ev) if (cudaEventCreate(&ev) != cudaSuccess) rc = fail(MBOTS_ECUDA, "cudaEventCreate");
         for (auto &ev : s->evShift) if (cudaEventCreate(&ev) != cudaSuccess) rc = fail(MBOTS_ECUDA, "cudaEventCreate");
         if (cudaEventCreateWithFlags(&s->evTotals, cudaEventDisableTiming) != cudaSuccess) rc = fail(MBOTS_ECUDA, "cudaEventCreate");
+        if (cudaStreamCreateWithFlags(&s->capStream, cudaStreamNonBlocking) != cudaSuccess) rc = fail(MBOTS_ECUDA, "cudaStreamCreate");
+        const char *g = getenv("MBOTS_GRAPHS");
+        s->useGraphs = !(g && g[0] == '0');
     }
     if (rc == MBOTS_OK) {
-        size_t sm1 = step_smem_bytes(cap), sm2 = export_smem_bytes(cap, 8, false);
-        (void)sm1; (void)sm2;   /* both far below the 48 KB default limit for cap <= 1024 */
+        prepare_kernels(s->d);                  /* shared-memory opt-in for the largest geometry, once, outside any capture */
         /* Sim::Sim for every world, then the first row assignment (no sensor pass: the
          * reference's tensors are only meaningful after the first step()). */
         launch_init(s->d, 0);
@@ -302,6 +410,32 @@ int mbots_step_async(mbots_sim *s, void *stream)
     if (!s) return fail(MBOTS_EINVAL, "null handle");
     DeviceGuard g(s->device);
     return enqueue_step(s, (cudaStream_t)stream);
+}
+
+int mbots_rollout_step_async(mbots_sim *s, const int32_t *actions_dev, uint64_t action_rows, int32_t shift, void *stream)
+{
+    if (!s) return fail(MBOTS_EINVAL, "null handle");
+    DeviceGuard g(s->device);
+    return enqueue_step(s, (cudaStream_t)stream, actions_dev, action_rows, shift != 0);
+}
+
+int mbots_write_actions(mbots_sim *s, const int32_t *actions_dev, uint64_t action_rows, void *stream)
+{
+    if (!s || !actions_dev) return fail(MBOTS_EINVAL, "null argument");
+    DeviceGuard g(s->device);
+    uint32_t rows = s->hTotals->totalAgents;
+    if (s->dirty) rows += rows / 4u + 1024u;
+    launch_action_write(s->d, s->cur, actions_dev, action_rows, rows, (cudaStream_t)stream);
+    CU(cudaGetLastError());
+    s->launches += 1;
+    return MBOTS_OK;
+}
+
+int mbots_graph_launch_count(mbots_sim *s, uint64_t *out)
+{
+    if (!s || !out) return fail(MBOTS_EINVAL, "null argument");
+    *out = s->graphLaunches;
+    return MBOTS_OK;
 }
 
 int mbots_sync(mbots_sim *s, void *stream)
@@ -626,6 +760,8 @@ int mbots_load_state(mbots_sim *s, const void *host, uint64_t bytes, void *strea
     CU(cudaMemcpyAsync(s->d.totals, &h.totals, sizeof(Totals), cudaMemcpyHostToDevice, st));
     CU(cudaStreamSynchronize(st));
     s->d.worldIdOffset = h.worldIdOffset; s->d.seed = h.seed;
+    for (auto &kv : s->graphs) cudaGraphExecDestroy(kv.second);      /* the SimDev is baked into every kernel node */
+    s->graphs.clear();
     s->cur = 0;
     *s->hTotals = h.totals;
     s->totalAgents = h.totalAgents;

@@ -79,11 +79,13 @@ struct SimDev {
 };
 
 /* launchers (sim_kernels.cu) */
+void prepare_kernels(const SimDev &d);
 void launch_init(const SimDev &d, cudaStream_t s);
 void launch_step(const SimDev &d, int cur, uint32_t slots, cudaStream_t s);
 void launch_scan(const SimDev &d, int cur, int count_step, cudaStream_t s);
 int launch_export(const SimDev &d, int cur, int with_sensors, uint32_t bound, cudaStream_t s);
 void launch_shift(const SimDev &d, int cur, uint32_t rows_upper, cudaStream_t s);
+void launch_action_write(const SimDev &d, int cur, const void *src, unsigned long long src_rows, uint32_t rows_upper, cudaStream_t s);
 void launch_stats_reduce(const SimDev &d, long long *out16, cudaStream_t s);
 void launch_debug_gather(const SimDev &d, int what, void *out, cudaStream_t s);
 /* launchers (policy_kernels.cu) */

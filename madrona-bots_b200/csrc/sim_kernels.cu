@@ -23,6 +23,7 @@
  */
 #include <cuda_runtime.h>
 #include <stdint.h>
+#include <stdlib.h>
 #include "sim_dev.h"
 #include "sim_prims.cuh"
 
@@ -653,10 +654,14 @@ __device__ __forceinline__ void carry_column(void *dst, const void *src, const i
     }
 }
 
-/* One world, one warp. `my` = this warp's shared memory (export_layout). */
+/* One world, one warp -- or, for small launches, `nsplit` independent single-warp CTAs per world: every one of them
+ * stages the whole world in its own shared memory (cheap: one pose per agent), then exports, carries and senses only its
+ * share [n * split / nsplit, n * (split + 1) / nsplit) of the agents. No synchronisation between the parts; a step of a
+ * small launch is then not bounded by one warp walking a whole world's sensor pass.
+ * `my` = this warp's shared memory (export_layout). */
 template <bool FAST>
 __device__ __forceinline__ void export_world(const SimDev &d, int cur, int with_sensors, uint32_t slots, uint32_t tile,
-                                             uint32_t w, int n, unsigned char *my)
+                                             uint32_t w, int n, unsigned char *my, int split, int nsplit)
 {
     typedef Sense<FAST> S;
     typedef typename S::Key Key;
@@ -680,6 +685,7 @@ __device__ __forceinline__ void export_world(const SimDev &d, int cur, int with_
     const int off = d.worldOffset[w];
     const float4 srew = d.speciesReward[w];
     const unsigned lt = (1u << lane) - 1u;
+    const int a_lo = (n * split) / nsplit, a_hi = (n * (split + 1)) / nsplit;   /* this part's agents */
 
     if (FAST && lane == 0) spec[63] = 0xffu;            /* species byte a missed ray decodes to (n <= 63) */
     /* ---- per agent (one lane each): new row, observation exports, small carried columns ---- */
@@ -706,11 +712,12 @@ __device__ __forceinline__ void export_world(const SimDev &d, int cur, int with_
         if (on) {
             const int row = comp(rb, sp - 1) + rank;
             const int old = __float_as_int(sc.x);
+            const bool mine = s >= a_lo && s < a_hi;
             /* carried small columns: issue the loads first */
             int4 pst = make_int4(0, 0, 0, 0);
             float2 ppos = make_float2(0.f, 0.f), psur = make_float2(0.f, 0.f);
             float prew = 0.f, phl = 0.f;
-            if (old >= 0) {
+            if (old >= 0 && mine) {
                 pst = reinterpret_cast<const int4 *>(from.prev_stats)[old];
                 ppos = reinterpret_cast<const float2 *>(from.prev_position)[old];
                 psur = reinterpret_cast<const float2 *>(from.prev_surrounding)[old];
@@ -724,34 +731,38 @@ __device__ __forceinline__ void export_world(const SimDev &d, int cur, int with_
             const Dir hd = cull_heading(Rot{p.z, p.w});
             head[s] = make_float2(hd.x, hd.y);
             spec[s] = (uint8_t)sp;
-            /* updateObservations (:687-717), rewardSystem (:943-956), SensorOutputIndex (:783-784) */
-            const uint32_t st = (uint32_t)__float_as_int(sc.w);
-            reinterpret_cast<float2 *>(to.position)[row] = make_float2(p.x, p.y);
-            to.health[row] = (float)hp;
-            reinterpret_cast<float2 *>(to.surrounding)[row] = make_float2(sc.y, sc.z);
-            reinterpret_cast<int4 *>(to.stats)[row] = make_int4(st & 1u, (st >> 1) & 1u, (st >> 2) & 1u, (st >> 3) & 1u);
-            const float sterm = sp == 1 ? srew.x : sp == 2 ? srew.y : sp == 3 ? srew.z : srew.w;
-            to.reward[row] = with_sensors ? agent_reward(sterm, hp, (st & 4u) != 0, (st & 8u) != 0, (st & 2u) != 0) : 0.f;
-            d.sensorIndex[off + s] = row;
-            d.row[base + s] = row;
-            if (!with_sensors) d.target[base + s] = (int16_t)-1;
-            reinterpret_cast<int4 *>(to.prev_stats)[row] = pst;
-            reinterpret_cast<float2 *>(to.prev_position)[row] = ppos;
-            reinterpret_cast<float2 *>(to.prev_surrounding)[row] = psur;
-            to.prev_reward[row] = prew;
-            to.prev_health[row] = phl;
+            if (mine) {
+                /* updateObservations (:687-717), rewardSystem (:943-956), SensorOutputIndex (:783-784) */
+                const uint32_t st = (uint32_t)__float_as_int(sc.w);
+                reinterpret_cast<float2 *>(to.position)[row] = make_float2(p.x, p.y);
+                to.health[row] = (float)hp;
+                reinterpret_cast<float2 *>(to.surrounding)[row] = make_float2(sc.y, sc.z);
+                reinterpret_cast<int4 *>(to.stats)[row] = make_int4(st & 1u, (st >> 1) & 1u, (st >> 2) & 1u, (st >> 3) & 1u);
+                const float sterm = sp == 1 ? srew.x : sp == 2 ? srew.y : sp == 3 ? srew.z : srew.w;
+                to.reward[row] = with_sensors ? agent_reward(sterm, hp, (st & 4u) != 0, (st & 8u) != 0, (st & 2u) != 0) : 0.f;
+                d.sensorIndex[off + s] = row;
+                d.row[base + s] = row;
+                if (!with_sensors) d.target[base + s] = (int16_t)-1;
+                reinterpret_cast<int4 *>(to.prev_stats)[row] = pst;
+                reinterpret_cast<float2 *>(to.prev_position)[row] = ppos;
+                reinterpret_cast<float2 *>(to.prev_surrounding)[row] = psur;
+                to.prev_reward[row] = prew;
+                to.prev_health[row] = phl;
+            }
         }
     }
     __syncwarp();
 
     /* ---- the sort: the wide columns of the observation record follow their agent ---- */
-    carry_column<float4, 4, 3>(to.hidden, from.hidden, newrow, oldrow, n, lane);
-    carry_column<float4, 4, 3>(to.prev_hidden, from.prev_hidden, newrow, oldrow, n, lane);
-    carry_column<int2, 3, 4>(to.action, from.action, newrow, oldrow, n, lane);
-    carry_column<int2, 3, 4>(to.prev_action, from.prev_action, newrow, oldrow, n, lane);
+    const int na = a_hi - a_lo;
+    const int *nr = newrow + a_lo, *orow = oldrow + a_lo;
+    carry_column<float4, 4, 3>(to.hidden, from.hidden, nr, orow, na, lane);
+    carry_column<float4, 4, 3>(to.prev_hidden, from.prev_hidden, nr, orow, na, lane);
+    carry_column<int2, 3, 4>(to.action, from.action, nr, orow, na, lane);
+    carry_column<int2, 3, 4>(to.prev_action, from.prev_action, nr, orow, na, lane);
     /* updateSensorOutputIdx (:774-780): last frame's sensor rows become the prev rows */
-    carry_column<int4, 2, 3>(to.prev_semantic, from.semantic, newrow, oldrow, n, lane);
-    carry_column<int4, 2, 3>(to.prev_depth, from.depth, newrow, oldrow, n, lane);
+    carry_column<int4, 2, 3>(to.prev_semantic, from.semantic, nr, orow, na, lane);
+    carry_column<int4, 2, 3>(to.prev_depth, from.depth, nr, orow, na, lane);
 
     if (!with_sensors) return;
 
@@ -768,8 +779,8 @@ __device__ __forceinline__ void export_world(const SimDev &d, int cur, int with_
      *     ties go to the lowest slot, and the order in which candidates are tested does not matter.
      *  4. one lane per (observer, 4 rays): decode, write 4 depth + 4 semantic bytes, finder hit */
     constexpr int JB = S::kJBits;
-    for (int tile0 = 0; tile0 < n; tile0 += (int)tile) {
-        const int m = min((int)tile, n - tile0);
+    for (int tile0 = a_lo; tile0 < a_hi; tile0 += (int)tile) {
+        const int m = min((int)tile, a_hi - tile0);
         {
             uint4 *b4 = reinterpret_cast<uint4 *>(best);
             const int vecs = m * kSensor * (int)sizeof(Key) / 16;
@@ -927,23 +938,24 @@ __device__ __forceinline__ void export_world(const SimDev &d, int cur, int with_
  *               worlds with a small grid, and nothing at all when no world is that large). */
 template <bool FAST>
 __global__ void __launch_bounds__(kExportWarps * 32, FAST ? kExportFastMinBlocks : 16 / kExportWarps)
-export_kernel(SimDev d, int cur, int with_sensors, uint32_t slots, uint32_t tile, int skip_upto)
+export_kernel(SimDev d, int cur, int with_sensors, uint32_t slots, uint32_t tile, int skip_upto, int split_log2)
 {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     const int warp = threadIdx.x >> 5;
     if (!FAST && skip_upto >= 0 && (int)d.totals->maxWorldCount <= skip_upto) return;
     unsigned char *my = smem_raw + (size_t)export_layout(slots, tile, sizeof(typename Sense<FAST>::Key)).total * warp;
     if (FAST) {
-        const uint32_t w = blockIdx.x * kExportWarps + warp;    /* one world per warp */
+        const uint32_t unit = blockIdx.x * kExportWarps + warp;  /* one (world, part) per warp */
+        const uint32_t w = unit >> split_log2;
         if (w >= d.numWorlds) return;               /* whole warp: no block-level barrier anywhere */
         const int n = d.worldCount[w];
         if (n > (int)slots || n > 63) return;       /* slot 63 is the miss sentinel of the 32-bit keys */
-        export_world<FAST>(d, cur, with_sensors, slots, tile, w, n, my);
+        export_world<FAST>(d, cur, with_sensors, slots, tile, w, n, my, (int)(unit & ((1u << split_log2) - 1u)), 1 << split_log2);
     } else {
         for (uint32_t w = blockIdx.x * kExportWarps + warp; w < d.numWorlds; w += gridDim.x * kExportWarps) {
             const int n = d.worldCount[w];
             if (n <= skip_upto) continue;
-            export_world<FAST>(d, cur, with_sensors, slots, tile, w, n, my);
+            export_world<FAST>(d, cur, with_sensors, slots, tile, w, n, my, 0, 1);
             __syncwarp();
         }
     }
@@ -1019,6 +1031,38 @@ __global__ void __launch_bounds__(256, MBK_SHIFT_MIN_BLOCKS) shift_kernel(SimDev
 }
 
 /* ------------------------------------------------------------------------- */
+/* action_write_kernel: the caller's action rows -> the action export, row count   */
+/* resolved ON THE DEVICE (totals->totalAgents), so that a host that keeps its     */
+/* actions (or its policy) on the GPU never has to wait for a step to learn how    */
+/* many rows to write (learn/training_loop.py:136 writes them through the view).   */
+
+__global__ void __launch_bounds__(256) action_write_kernel(SimDev d, int cur, const int2 *__restrict__ src, unsigned long long src_rows)
+{
+    unsigned long long rows = d.totals->totalAgents;
+    if (rows > src_rows) rows = src_rows;
+    int2 *dst = reinterpret_cast<int2 *>(d.obs[cur].action);
+    const size_t n = (size_t)rows * 3, stride = (size_t)gridDim.x * blockDim.x;
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += 4 * stride) {
+        int2 v[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u)
+            if (i + u * stride < n) v[u] = src[i + u * stride];
+#pragma unroll
+        for (int u = 0; u < 4; ++u)
+            if (i + u * stride < n) dst[i + u * stride] = v[u];
+    }
+}
+
+void launch_action_write(const SimDev &d, int cur, const void *src, unsigned long long src_rows, uint32_t rows_upper, cudaStream_t s)
+{
+    size_t vecs = (size_t)rows_upper * 3;
+    size_t blocks = (vecs + 256 * 4 - 1) / (256 * 4);
+    if (blocks > 148 * 8) blocks = 148 * 8;
+    if (blocks == 0) blocks = 1;
+    action_write_kernel<<<(unsigned)blocks, 256, 0, s>>>(d, cur, reinterpret_cast<const int2 *>(src), src_rows);
+}
+
+/* ------------------------------------------------------------------------- */
 /* episode statistics and debug gathers (not on the hot path)                  */
 
 /* out[16] must be zero on entry; every CTA adds its share */
@@ -1074,13 +1118,30 @@ void launch_init(const SimDev &d, cudaStream_t s)
     init_kernel<<<d.numWorlds, threads, 0, s>>>(d);
 }
 
+/* Dynamic shared memory above 48 KB needs an opt-in per kernel: done once per handle for the largest geometry the
+ * handle can ask for (its capacity), outside any stream capture. */
+void prepare_kernels(const SimDev &d)
+{
+    static size_t granted[64][2];                       /* per device: never shrink what an earlier handle asked for */
+    int dev = 0;
+    cudaGetDevice(&dev);
+    dev &= 63;
+    const size_t s1 = step_smem_bytes(d.cap), s2 = export_smem_bytes(d.cap, kFullTile, false);
+    if (s1 > 48 * 1024 && s1 > granted[dev][0]) {
+        cudaFuncSetAttribute(step_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)s1);
+        granted[dev][0] = s1;
+    }
+    if (s2 > 48 * 1024 && s2 > granted[dev][1]) {
+        cudaFuncSetAttribute(export_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)s2);
+        granted[dev][1] = s2;
+    }
+}
+
 void launch_step(const SimDev &d, int cur, uint32_t slots, cudaStream_t s)
 {
     /* slots: a bound on the live agents of any world before the step; the capacity always is one */
     if (slots == 0 || slots > d.cap) slots = d.cap;
     const size_t smem = step_smem_bytes(slots);
-    if (smem > 48 * 1024)
-        cudaFuncSetAttribute(step_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     step_kernel<<<(d.numWorlds + kStepWarps - 1) / kStepWarps, kStepWarps * 32, smem, s>>>(d, cur, slots);
 }
 
@@ -1093,14 +1154,28 @@ void launch_scan(const SimDev &d, int cur, int count_step, cudaStream_t s)
 
 template <bool FAST>
 static void launch_export_variant(const SimDev &d, int cur, int with_sensors, uint32_t slots, uint32_t tile, int skip_upto,
-                                  cudaStream_t s)
+                                  int split_log2, cudaStream_t s)
 {
     const size_t smem = export_smem_bytes(slots, tile, FAST);
-    if (smem > 48 * 1024)
-        cudaFuncSetAttribute(export_kernel<FAST>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    uint32_t grid = (d.numWorlds + kExportWarps - 1) / kExportWarps;
+    uint32_t grid = ((d.numWorlds << split_log2) + kExportWarps - 1) / kExportWarps;
     if (!FAST && skip_upto >= 0 && grid > 148u * 4u) grid = 148u * 4u;   /* clean-up pass: few worlds, if any */
-    export_kernel<FAST><<<grid, kExportWarps * 32, smem, s>>>(d, cur, with_sensors, slots, tile, skip_upto);
+    export_kernel<FAST><<<grid, kExportWarps * 32, smem, s>>>(d, cur, with_sensors, slots, tile, skip_upto, split_log2);
+}
+
+/* Parts per world of the FAST export kernel (log2): a full GPU wants ~32 resident single-warp CTAs per SM; below that a
+ * world is split over 2, 4 or 8 CTAs so that the launch is not bounded by one warp walking a whole world's sensor pass.
+ * MBOTS_EXPORT_SPLIT_LOG2 overrides (0..3). */
+static int export_split_log2(uint32_t numWorlds)
+{
+    static int forced = -2;
+    if (forced == -2) {
+        const char *e = getenv("MBOTS_EXPORT_SPLIT_LOG2");
+        forced = e ? atoi(e) : -1;
+        if (forced < 0 || forced > 3) forced = -1;
+    }
+    if (forced >= 0) return forced;
+    const uint32_t per_sm = numWorlds / 148u;
+    return per_sm >= 64u ? 0 : per_sm >= 24u ? 1 : per_sm >= 8u ? 2 : 3;
 }
 
 /* bound: the largest world the caller expects after this step (0 = unknown). Worlds above it are still
@@ -1109,15 +1184,15 @@ int launch_export(const SimDev &d, int cur, int with_sensors, uint32_t bound, cu
 {
     uint32_t fast_slots = (bound + 7u) & ~7u;
     if (bound == 0 || fast_slots > (uint32_t)kFastSlots || fast_slots > d.cap) {
-        launch_export_variant<false>(d, cur, with_sensors, d.cap, kFullTile, -1, s);
+        launch_export_variant<false>(d, cur, with_sensors, d.cap, kFullTile, -1, 0, s);
         return 1;
     }
     /* 32 observers per sensor tile: 56 slots + 4 KB of keys = 6.1 KB per single-warp CTA, 32 of them per SM.
      * (One tile for the whole world -- 40 observers, 26-28 CTAs per SM -- measured 1 % slower.) */
     uint32_t tile = (uint32_t)MBK_EXPORT_FAST_TILE;
     if (tile > fast_slots) tile = fast_slots;
-    launch_export_variant<true>(d, cur, with_sensors, fast_slots, tile, 0, s);
-    launch_export_variant<false>(d, cur, with_sensors, d.cap, kFullTile, (int)(fast_slots < 63u ? fast_slots : 63u), s);
+    launch_export_variant<true>(d, cur, with_sensors, fast_slots, tile, 0, export_split_log2(d.numWorlds), s);
+    launch_export_variant<false>(d, cur, with_sensors, d.cap, kFullTile, (int)(fast_slots < 63u ? fast_slots : 63u), 0, s);
     return 2;
 }
 

@@ -112,6 +112,27 @@ class SimManager:
     def step_async(self):
         _native.check(self._lib.mbots_step_async(self._h, self._stream()), "mbots_step_async")
 
+    def rollout_step_async(self, actions=None, shift=True):
+        """One launch: [write `actions` (a contiguous CUDA int32 (rows, 6) tensor in observation-row order; only the live
+        rows are written, the count is read on the device)] -> step + sensor -> [shift_observations]. Nothing is waited
+        for: the host may enqueue the next step at once (`sync()` waits for the last one)."""
+        ptr, rows = None, 0
+        if actions is not None:
+            assert actions.is_cuda and actions.is_contiguous() and actions.dim() == 2 and actions.shape[1] == 6
+            ptr, rows = ctypes.c_void_p(actions.data_ptr()), int(actions.shape[0])
+        _native.check(self._lib.mbots_rollout_step_async(self._h, ptr, rows, 1 if shift else 0, self._stream()),
+                      "mbots_rollout_step_async")
+
+    def write_actions(self, actions):
+        assert actions.is_cuda and actions.is_contiguous() and actions.dim() == 2 and actions.shape[1] == 6
+        _native.check(self._lib.mbots_write_actions(self._h, ctypes.c_void_p(actions.data_ptr()), int(actions.shape[0]),
+                                                    self._stream()), "mbots_write_actions")
+
+    def graph_launch_count(self):
+        out = ctypes.c_uint64()
+        _native.check(self._lib.mbots_graph_launch_count(self._h, ctypes.byref(out)), "mbots_graph_launch_count")
+        return out.value
+
     def sync(self):
         _native.check(self._lib.mbots_sync(self._h, self._stream()), "mbots_sync")
 

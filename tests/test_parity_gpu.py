@@ -313,3 +313,99 @@ def test_async_step_shift_then_sync_matches_oracle(cuda_device):
     g.step_async(); g.shift_observations_async(); g.sync()
     ms = g.profile_read()
     assert all(v["calls"] >= 1 for k, v in ms.items() if k in ("step", "export_sense")), ms
+
+
+@pytest.mark.parametrize("worlds,depth", [(96, 1), (96, 6), (2500, 4)])
+def test_rollout_step_graph_and_run_ahead_match_oracle(cuda_device, worlds, depth):
+    """mbots_rollout_step_async: action write (row count resolved on the device) + step + shift as one CUDA graph
+    launch, with up to `depth` steps enqueued before the host waits (launch geometry then comes from stale totals
+    plus slack). The oracle, fed the same action rows, must agree on every export whenever the host catches up."""
+    import torch
+    from oracle_binding import random_actions
+    o, g = make_pair(worlds, 33, 32)
+    rng = np.random.default_rng(9)
+    rows_cap = worlds * 64
+    t = 0
+    for rnd in range(8):
+        bufs = []
+        for k in range(depth):
+            A = o.num_agents()
+            acts = random_actions(rng, A, "bits" if rnd % 2 else "onehot")
+            o.tensor("ACTION")[:] = acts
+            o.step(); o.shift_observations()
+            dev = torch.full((rows_cap, 6), 7, dtype=torch.int32, device="cuda")     # rows beyond the live count are ignored
+            dev[:A] = torch.from_numpy(acts).cuda()
+            bufs.append(dev)                                                          # stays alive until the sync below
+            g.rollout_step_async(dev, shift=True)
+            t += 1
+        g.sync()
+        torch.cuda.synchronize()
+        compare(o, g, f"graph step {t} (depth {depth})")
+    assert g.graph_launch_count() == t
+    st = o.episode_stats()
+    assert st[10] > 0 and st[11] > 0
+
+
+def test_graphs_and_plain_launches_agree(cuda_device):
+    """The graph path (default), per-kernel timing (plain launches with events) and the blocking step() interleave
+    freely on one handle."""
+    import torch
+    from oracle_binding import random_actions
+    o, g = make_pair(64, 2, 32)
+    rng = np.random.default_rng(4)
+    for t in range(30):
+        A = o.num_agents()
+        acts = random_actions(rng, A, "onehot")
+        o.tensor("ACTION")[:] = acts
+        o.step(); o.shift_observations()
+        g.profile(t % 3 == 1)
+        dev = torch.from_numpy(acts).cuda()
+        if t % 3 == 2:
+            g.write_actions(dev); g.step(); g.shift_observations()
+        else:
+            g.rollout_step_async(dev, shift=True); g.sync()
+        torch.cuda.synchronize()
+        compare(o, g, f"mixed step {t}")
+
+
+class _GpuRefAdapter:
+    """One world on the CUDA path behind the surface tests/golden/make_refsim_golden.run_case drives."""
+
+    def __init__(self, seed, world_id, init):
+        from madrona_bots import SimManager
+        self.sim = SimManager(0, 1, seed, init, world_id_offset=world_id)
+
+    def num_agents(self):
+        return self.sim.num_agents()
+
+    def tensor(self, name):
+        return gpu_np(self.sim, name)
+
+    def write(self, name, value):
+        import torch
+        if len(value):
+            self.sim.export(name).to_torch().copy_(torch.from_numpy(value))
+
+    def step(self):
+        self.sim.step()
+
+    def shift_observations(self):
+        self.sim.shift_observations()
+
+
+@pytest.mark.parametrize("name", ["s0_w0", "s7_w3_bits", "s21_w4099", "s9_w1_init13", "s5_w2_init48"])
+def test_cuda_path_reproduces_reference_text_rollouts(cuda_device, name):
+    """tests/golden/refsim_rollouts.npz holds per-step digests of every export of worlds run from the REFERENCE'S
+    OWN SOURCE TEXT (src/sim/sim.cpp, M/src/render/ecs_system.cpp, M/src/mw/device/bvh_raycast.cpp under the host
+    mock of oracle/refmock/; generator: tests/golden/make_refsim_golden.py). The CUDA path alone -- no oracle, no
+    reference on this box -- must reproduce them bit for bit."""
+    import os
+    import sys
+    sys.path.insert(0, os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden"))
+    from make_refsim_golden import CASES, run_case
+    from refsim_binding import REF_EXPORTS
+    gold = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "refsim_rollouts.npz"))
+    sim, counts, digs = run_case(_GpuRefAdapter, CASES[name])
+    np.testing.assert_array_equal(counts, gold[name + ".counts"])
+    bad = np.argwhere(digs != gold[name + ".digests"])
+    assert len(bad) == 0, f"first mismatch: step {bad[0][0]}, export {REF_EXPORTS[bad[0][1]]}"
