@@ -5,11 +5,14 @@
 
 One "step" = what learn/training_loop.py does to the simulator per epoch: write one action row per
 live agent, SimManager.step() (Step + Sensor task graphs), SimManager.shift_observations().
-Workload (config.workload): 65,536 independent worlds x 32 initial agents PER GPU (the configuration
-BASELINE.json's metric is quoted on; weak scaling: every rank owns its own 65,536 global world ids),
-uniform random one-hot actions from a pre-generated pool, seed 0.
+Workload (config.workload): 65,536 independent worlds x 32 initial agents IN TOTAL, sharded over the GPUs
+(BASELINE.json metric / configs[3]: strong scaling, 65,536 // N worlds per GPU, rank r owns global world ids
+[r * W/N, (r+1) * W/N)); uniform random one-hot actions from a pre-generated pool, seed 0. Multi-GPU runs add a
+companion leg with 65,536 worlds on EVERY GPU under the key weak_65536_per_gpu.
 
-  value        agent-steps/s, action pool resident in HBM (device-to-device write of the action rows)
+  value        agent-steps/s, action pool resident in HBM: one CUDA-graph launch per step (action write with the
+               row count resolved on the device, step + sensor, shift), the host up to 3 steps ahead of the device
+  value_sync_per_step  same work with the reference's blocking cadence (the host waits for every step)
   e2e          same loop driven through the C-ABI with HOST buffers: per step the action rows are
                copied from pinned host memory and the observation exports the caller reads
                (depth, semantic, position, health, surrounding, reward, species counts) are copied back;
@@ -45,14 +48,9 @@ POOL = 4                       # pre-generated action buffers, cycled
 # ALGORITHMIC bytes per agent-step (DESIGN.md "Algorithmic bytes"; SURVEY.md section 8(d) rows assigned
 # to the kernel that owns them). STEP_BYTES = 321 in total.
 ALGO_BYTES = {"step": 24 + 28 + 24 + 9.0, "export_sense": 44 + 64 + 64 + 64, "shift": 264}
-# bytes the export kernel really has to move per agent given that rows move every step:
-MOVED_BYTES_EXPORT = 280 + 280 + 36 + 64 + 4 + 2 + 41
-# dram__bytes_read.sum + dram__bytes_write.sum of export_kernel<FAST> per agent, from the committed
-# `ncu --set full` capture (profiles/r1k_ncu_full_summary.txt: 705.5 MB + 808.9 MB at 2,173,116 agents)
-NCU_TRAFFIC_BYTES_PER_AGENT_EXPORT = (705.549568e6 + 808.883200e6) / 2173116.0
-# same capture: what actually bounds the kernel is instruction issue
-NCU_EXPORT_ISSUE = {"warp_instructions_per_world": 445786274 / 65536.0, "issue_active_frac": 0.765}
-
+# the fused rollout step: the export kernel also leaves prev := cur (the shift call's 132 B read + 132 B written per agent)
+ALGO_BYTES["export_sense_fused_shift"] = ALGO_BYTES["export_sense"] + ALGO_BYTES["shift"]
+# measured DRAM traffic and warp instructions come from profiles/ncu_capture.json (ncu_capture() below), never from constants
 
 def measured_peaks():
     path = os.path.join(ROOT, "MEASURED_PEAKS.json")
@@ -222,11 +220,14 @@ def run_reference(args, rank, world):
 
 
 def workload_config(args, sample=None):
-    c = {"workload": f"{args.worlds_per_gpu} worlds x {INIT_AGENTS} initial agents per GPU, random one-hot actions, "
-                     "step + sensor + shift_observations per step, one host synchronisation per step",
+    c = {"workload": f"{args.worlds_per_gpu} worlds x {INIT_AGENTS} initial agents per GPU "
+                     f"({args.worlds_per_gpu * args.gpus} worlds in total, {args.scaling} scaling), random one-hot actions, "
+                     "action write + step + sensor + shift_observations per step as one CUDA-graph launch, host up to 3 steps ahead",
          "worlds_per_gpu": args.worlds_per_gpu, "init_agents_per_world": INIT_AGENTS, "seed": SEED,
          "sharding": f"worlds x{args.gpus} (independent worlds, no data-path collective)",
-         "l2": "per-step working set (~1.5 GB at 65,536 worlds) exceeds the 126 MB L2; no explicit flush"}
+         "l2": f"per-step working set (~{args.worlds_per_gpu * 24 // 1000} MB: two row sets + state) "
+               + ("exceeds the 126 MB L2; no explicit flush" if args.worlds_per_gpu >= 8192 else
+                  "fits the 126 MB L2 at this size: steps run warm, as they do in a rollout")}
     if sample:
         c["sample"] = sample
     return c
@@ -281,6 +282,97 @@ def bind_host_to_gpu(local_rank):
 
 
 # ------------------------------------------------------------------------------------------------
+def source_sha():
+    """Hash of the kernel sources an ncu capture belongs to (profiles/ncu_capture.json is only trusted for the code it saw)."""
+    import hashlib
+    h = hashlib.sha256()
+    for f in ("sim_kernels.cu", "sim_prims.cuh", "sim_dev.h"):
+        with open(os.path.join(ROOT, "madrona-bots_b200", "csrc", f), "rb") as fh:
+            h.update(fh.read())
+    return h.hexdigest()[:16]
+
+
+def ncu_capture():
+    """profiles/ncu_capture.json (written by tools/ncu_capture_json.py from an `ncu --set full` report of this very code):
+    per kernel the DRAM bytes and warp instructions of one launch. None when absent or taken from other sources."""
+    try:
+        with open(os.path.join(ROOT, "profiles", "ncu_capture.json")) as f:
+            cap = json.load(f)
+    except Exception:
+        return None, "no capture (profiles/ncu_capture.json missing)"
+    if cap.get("source_sha") != source_sha():
+        return None, f"STALE capture: taken from sources {cap.get('source_sha')}, this tree is {source_sha()} -- re-run tools/gpu_ncu_capture.sh"
+    return cap, "profiles/ncu_capture.json (same sources)"
+
+
+class Leg:
+    """K-step timed regions, repeated until ~0.25 s of device time has been measured; the median repeat is reported."""
+
+    def __init__(self, world, dev):
+        self.world, self.dev = world, dev
+
+    def barrier(self):
+        import torch
+        import torch.distributed as dist
+        torch.cuda.synchronize()
+        if self.world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def run(self, sim, step_fn, finish_fn, steps, first_index, max_repeats=20, min_seconds=0.25):
+        import torch
+        from madrona_bots.sharding import allreduce_max, allreduce_stats
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        out, idx, repeats = [], first_index, None
+        while repeats is None or len(out) < repeats:
+            self.barrier()
+            st0 = sim.episode_stats()
+            e0.record()
+            for i in range(steps):
+                step_fn(idx + i)
+            finish_fn()
+            e1.record()
+            self.barrier()
+            idx += steps
+            st1 = sim.episode_stats()
+            ms = allreduce_max(e0.elapsed_time(e1), device=self.dev)
+            tot = allreduce_stats([b - a for a, b in zip(st0, st1)], device=self.dev)     # NCCL: the only collective of the path
+            out.append({"ms": ms, "agent_steps": tot[0], "local_agent_steps": st1[0] - st0[0], "stats": tot})
+            if repeats is None:
+                repeats = int(min(max_repeats, max(1, -(-min_seconds * 1e3 // max(ms, 1e-3)))))
+        rates = sorted(range(len(out)), key=lambda k: out[k]["agent_steps"] / out[k]["ms"])
+        med = out[rates[len(rates) // 2]]
+        med = dict(med, repeats=len(out), value=med["agent_steps"] / (med["ms"] * 1e-3),
+                   spread=[out[rates[0]]["agent_steps"] / (out[rates[0]]["ms"] * 1e-3),
+                           out[rates[-1]]["agent_steps"] / (out[rates[-1]]["ms"] * 1e-3)])
+        return med, idx
+
+
+def link_probe(dev, sizes, seconds=1.0):
+    """Pinned device-to-host copies of the e2e leg's sizes, nothing else running: what the host link of this rank
+    delivers while every rank probes at once (the ceiling of the e2e leg)."""
+    import torch
+    src = [torch.empty(n, dtype=torch.uint8, device=dev) for n in sizes]
+    dst = [torch.empty(n, dtype=torch.uint8).pin_memory() for n in sizes]
+    for a, b in zip(src, dst):
+        b.copy_(a, non_blocking=True)
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    reps, t0 = 0, time.perf_counter()
+    e0.record()
+    while time.perf_counter() - t0 < seconds:
+        for a, b in zip(src, dst):
+            b.copy_(a, non_blocking=True)
+        torch.cuda.synchronize()
+        reps += 1
+    e1.record()
+    torch.cuda.synchronize()
+    return sum(sizes) * reps / (e0.elapsed_time(e1) * 1e-3) / 1e9
+
+
+RUN_AHEAD = 3          # steps the host may have in flight in the device-resident leg
+
+
 def run_ours(args, rank, world, local_rank):
     import numpy as np
     import torch
@@ -295,54 +387,69 @@ def run_ours(args, rank, world, local_rank):
     W = args.worlds_per_gpu
     sim = SimManager(local_rank, W, SEED, INIT_AGENTS, world_id_offset=rank * W, max_agents_per_world=args.cap)
     rows_cap = W * 48                               # the population stays near 33 agents/world (max ~41)
+    leg = Leg(world, dev)
 
     host_pool = [torch.from_numpy(a).pin_memory() for a in one_hot_pool_numpy(rows_cap, 1234 + rank)]
     dev_pool = [a.to(dev, non_blocking=True) for a in host_pool]
     torch.cuda.synchronize()
 
-    def barrier():
-        torch.cuda.synchronize()
-        if world > 1:
-            dist.barrier()
-        torch.cuda.synchronize()
+    # ---------------- device-resident leg (value): one graph launch per step, host runs ahead ----------------
+    inflight = []
 
     def dev_step(i):
-        A = sim.num_agents()
-        assert A <= rows_cap, "action pool too small for the population"
-        sim.action_tensor(False).to_torch().copy_(dev_pool[i % POOL][:A])
-        sim.step_async()
-        sim.shift_observations_async()
-        sim.sync()                                    # one host synchronisation per step (the next step needs the row count)
+        # action rows of the pool -> action export (live row count read on the device) -> step + sensor -> shift:
+        # one CUDA graph launch; the host waits only when RUN_AHEAD steps are in flight
+        sim.rollout_step_async(dev_pool[i % POOL], shift=True)
+        ev = torch.cuda.Event()
+        ev.record()
+        inflight.append(ev)
+        if len(inflight) > RUN_AHEAD:
+            inflight.pop(0).synchronize()
 
-    # ---------------- device-resident leg (value) ----------------
+    def dev_finish():
+        sim.sync()
+        inflight.clear()
+
     for i in range(args.warmup):
         dev_step(i)
-    sim.profile(True)
-    barrier()
+    dev_finish()
+    assert sim.num_agents() <= rows_cap, "action pool too small for the population"
     sampler = ClockSampler(local_rank)
     if rank == 0:
         sampler.start()
-    st0 = sim.episode_stats()
-    l0 = sim.launch_count()
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    e0.record()
-    for i in range(args.steps):
-        dev_step(args.warmup + i)
-    e1.record()
-    barrier()
-    ms = e0.elapsed_time(e1)
+    l0, g0 = sim.launch_count(), sim.graph_launch_count()
+    res, idx = leg.run(sim, dev_step, dev_finish, args.steps, args.warmup)
+    launches_per_step = (sim.launch_count() - l0 - 2 * res["repeats"]) / (res["repeats"] * args.steps)   # minus the stats reads
+    graph_launches = sim.graph_launch_count() - g0
     if rank == 0:
-        sampler.pause()                               # resumed for the end-to-end leg's timed region
+        sampler.pause()
+
+    # the same steps with the reference's blocking call sequence: write, step() (waits), shift
+    def sync_step(i):
+        sim.write_actions(dev_pool[i % POOL])
+        sim.step_async()
+        sim.shift_observations_async()
+        sim.sync()
+
+    res_sync, idx = leg.run(sim, sync_step, lambda: None, args.steps, idx, max_repeats=5, min_seconds=0.1)
+
+    # per-kernel device times: the timed loop's own kernels with events between them (plain launches instead of the
+    # graph), then the unfused call sequence (separate shift pass) for comparison
+    sim.profile(True)
+    for i in range(args.steps):
+        sim.rollout_step_async(dev_pool[(idx + i) % POOL], shift=True)
+        sim.sync()
+    idx += args.steps
+    torch.cuda.synchronize()
     prof = sim.profile_read()
+    sim.profile(True)                                 # resets the accumulators
+    for i in range(args.steps):
+        sync_step(idx + i)
+    idx += args.steps
+    torch.cuda.synchronize()
+    prof_unfused = sim.profile_read()
     sim.profile(False)
-    st1 = sim.episode_stats()
-    launches = sim.launch_count() - l0 - 1          # minus the stats-reduce kernel of st0/st1 bookkeeping
-    local_agent_steps = st1[0] - st0[0]
-    delta = [b - a for a, b in zip(st0, st1)]
-    delta[1] = st1[1] - st0[1]
-    tot = allreduce_stats(delta, device=dev)          # NCCL: the only collective of the path
-    ms_max = allreduce_max(ms, device=dev)
-    value = tot[0] / (ms_max * 1e-3)
+    prof_agents = sim.num_agents()
 
     # ---------------- end-to-end leg (host buffers through the C-ABI) ----------------
     obs_names = [("SENSOR_DEPTH", 32), ("SENSOR_SEMANTIC", 32), ("POSITION", 8), ("HEALTH", 4), ("SURROUNDING", 8),
@@ -355,14 +462,13 @@ def run_ours(args, rank, world, local_rank):
     n_copy = max(1, int(os.environ.get("MBOTS_E2E_COPY_STREAMS", "1")))
     copy_streams = [torch.cuda.Stream(device=dev) for _ in range(n_copy)]
     drained = [None, None]                            # events: the drain that read row set (step % 2) is complete
-    h2d = d2h = 0
+    moved = {"h2d": 0, "d2h": 0}
 
     def e2e_step(i):
-        nonlocal h2d, d2h
         main = torch.cuda.current_stream()
         A = sim.num_agents()
         sim.copy_from_host("ACTION", host_pool[i % POOL].data_ptr(), A * 24)
-        h2d += A * 24
+        moved["h2d"] += A * 24
         if drained[i % 2] is not None:
             for ev in drained[i % 2]:
                 main.wait_event(ev)                   # this step's export overwrites the row set drained two steps ago
@@ -378,75 +484,133 @@ def run_ours(args, rank, world, local_rank):
             cs.wait_event(done)
         for k, (n, b) in enumerate(obs_names):
             sim.copy_to_host(n, host_out[i % 2][n].data_ptr(), A * b, stream=copy_streams[k % n_copy])
-            d2h += A * b
+            moved["d2h"] += A * b
         sim.copy_to_host("SPECIES_COUNT", host_sc[i % 2].data_ptr(), W * 16, stream=copy_streams[0])
-        d2h += W * 16
+        moved["d2h"] += W * 16
         drained[i % 2] = []
         for cs in copy_streams:
             ev = torch.cuda.Event()
             ev.record(cs)
             drained[i % 2].append(ev)
 
-    for i in range(min(args.warmup, 3)):
-        e2e_step(i)
-    h2d = d2h = 0
-    barrier()
-    se0 = sim.episode_stats()
+    def e2e_finish():
+        for cs in copy_streams:
+            torch.cuda.current_stream().wait_stream(cs)           # the last drain is inside the timed region
+
+    for i in range(3):
+        e2e_step(idx + i)
+    idx += 3
+    e2e_finish()
+    moved["h2d"] = moved["d2h"] = 0
     if rank == 0:
         sampler.resume()
-    e0.record()
-    for i in range(args.steps):
-        e2e_step(min(args.warmup, 3) + i)
-    for cs in copy_streams:
-        torch.cuda.current_stream().wait_stream(cs)           # the last drain is inside the timed region
-    e1.record()
-    barrier()
-    clocks = sampler.stop() if rank == 0 else None    # sampled during both timed regions (device-resident and end-to-end)
-    ms_e = allreduce_max(e0.elapsed_time(e1), device=dev)
-    se1 = sim.episode_stats()
-    tot_e = allreduce_stats([b - a for a, b in zip(se0, se1)], device=dev)
-    e2e_value = tot_e[0] / (ms_e * 1e-3)
+    res_e, idx = leg.run(sim, e2e_step, e2e_finish, args.steps, idx, max_repeats=5, min_seconds=0.2)
+    clocks = sampler.stop() if rank == 0 else None    # sampled during the device-resident and the end-to-end timed regions
+    e2e_steps = res_e["repeats"] * args.steps
+    d2h_per_step = moved["d2h"] // max(1, e2e_steps)
+    leg.barrier()
+    link = link_probe(dev, [prof_agents * b for _, b in obs_names] + [W * 16], seconds=1.0)
+    link_all = allreduce_stats([int(link * 1e6)], device=dev)[0] / 1e6 if world > 1 else link
+    link_min = -allreduce_max(-link, device=dev) if world > 1 else link
+
+    # ---------------- weak-scaling companion: 65,536 worlds on every GPU ----------------
+    weak = None
+    if world > 1 and args.scaling == "strong" and not args.no_weak_leg:
+        del sim
+        torch.cuda.empty_cache()
+        Ww = args.worlds
+        simw = SimManager(local_rank, Ww, SEED, INIT_AGENTS, world_id_offset=rank * Ww, max_agents_per_world=args.cap)
+        poolw = [torch.from_numpy(a).to(dev) for a in one_hot_pool_numpy(Ww * 48, 99 + rank)]
+        pend = []
+
+        def w_step(i):
+            simw.rollout_step_async(poolw[i % POOL], shift=True)
+            ev = torch.cuda.Event()
+            ev.record()
+            pend.append(ev)
+            if len(pend) > RUN_AHEAD:
+                pend.pop(0).synchronize()
+
+        def w_finish():
+            simw.sync()
+            pend.clear()
+
+        for i in range(args.warmup):
+            w_step(i)
+        w_finish()
+        rw, _ = leg.run(simw, w_step, w_finish, args.steps, args.warmup, max_repeats=5, min_seconds=0.1)
+        weak = {"value": rw["value"], "unit": UNIT, "ms_per_step": rw["ms"] / args.steps, "worlds_per_gpu": Ww,
+                "scaling": "weak", "repeats": rw["repeats"]}
 
     if rank != 0:
         return None
     peak, peak_src = measured_peaks()
-    agents_per_launch = local_agent_steps / max(1, args.steps)
+    agents_per_launch = res["local_agent_steps"] / max(1, args.steps)
     k_ms = prof["export_sense"]["ms"]
-    achieved = ALGO_BYTES["export_sense"] * agents_per_launch / (k_ms * 1e-3) / 1e9 if k_ms > 0 else 0.0
-    kernels = {}
-    for name in ("step", "scan", "export_sense", "shift"):
-        kms = prof[name]["ms"]
-        ent = {"ms": kms, "calls": prof[name]["calls"]}
-        if name in ALGO_BYTES and kms > 0:
-            ent["algo_gbs"] = ALGO_BYTES[name] * agents_per_launch / (kms * 1e-3) / 1e9
-            ent["frac"] = ent["algo_gbs"] / peak
-        kernels[name] = ent
+    algo_export = ALGO_BYTES["export_sense_fused_shift"]
+    achieved = algo_export * prof_agents / (k_ms * 1e-3) / 1e9 if k_ms > 0 else 0.0
+
+    def kernel_table(pr, names, algo):
+        out = {}
+        for name in names:
+            kms = pr[name]["ms"]
+            ent = {"ms": kms, "calls": pr[name]["calls"]}
+            if name in algo and kms > 0:
+                ent["algo_bytes_per_agent"] = algo[name]
+                ent["algo_gbs"] = algo[name] * prof_agents / (kms * 1e-3) / 1e9
+                ent["frac"] = ent["algo_gbs"] / peak
+            out[name] = ent
+        return out
+
+    kernels = kernel_table(prof, ("step", "scan", "export_sense"), dict(ALGO_BYTES, export_sense=algo_export))
+    kernels_unfused = kernel_table(prof_unfused, ("step", "scan", "export_sense", "shift"), ALGO_BYTES)
+    cap, cap_src = ncu_capture()
+    traffic = issue_frac = inst_per_world = None
+    sm_mhz = (clocks or {}).get("sm_mhz") or 1965.0
+    if cap and "export_kernel" in cap.get("kernels", {}):
+        ck = cap["kernels"]["export_kernel"]
+        traffic = (ck["dram_read_bytes"] + ck["dram_write_bytes"]) / ck["agents"] * prof_agents
+        inst_per_world = ck["warp_instructions"] / ck["worlds"]
+        if k_ms > 0:
+            issue_frac = inst_per_world * W / (k_ms * 1e-3) / (148 * 4 * sm_mhz * 1e6)
     line = {
-        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
-        "ms_per_step": ms_max / args.steps, "higher_is_better": True, "scaling": args.scaling, "vs_baseline": None,
+        "metric": METRIC, "value": res["value"], "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": res["ms"] / args.steps, "higher_is_better": True, "scaling": args.scaling, "vs_baseline": None,
         "dtype": "f32+i32", "data": "synthetic",
         "config": dict(workload_config(args), host_affinity=(f"rank bound to its GPU's {bound_cpus} local CPUs (NVML)"
                                                               if bound_cpus else "unchanged")),
-        "clocks": clocks, "gpu_launches": int(launches),
-        "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d // max(1, args.steps),
-                "d2h_bytes_per_step": d2h // max(1, args.steps), "ms_per_step": ms_e / args.steps,
-                "overlap": "device-to-host drain of step t on a copy stream under step t+1; all copies inside the timed region"},
-        "roofline": {"bound": "hbm", "kernel": "export_kernel (row carry + observation export + 32-ray sensor)",
+        "timing": {"repeats": res["repeats"], "reported": "median repeat of K steps", "spread": res["spread"],
+                   "run_ahead_steps": RUN_AHEAD},
+        "clocks": clocks, "gpu_launches": int(round(launches_per_step * args.steps)),
+        "launches_per_step": launches_per_step, "graph_launches": int(graph_launches),
+        "value_sync_per_step": {"value": res_sync["value"], "ms_per_step": res_sync["ms"] / args.steps,
+                                "what": "same work, the host waits for every step (write_actions, step_async, shift, sync): "
+                                        "the reference's blocking step() cadence"},
+        "e2e": {"value": res_e["value"], "unit": UNIT, "h2d_bytes_per_step": moved["h2d"] // max(1, e2e_steps),
+                "d2h_bytes_per_step": d2h_per_step, "ms_per_step": res_e["ms"] / args.steps,
+                "overlap": "device-to-host drain of step t on a copy stream under step t+1; all copies inside the timed region",
+                "link_gbs_measured": link, "link_gbs_all_ranks": link_all, "link_gbs_slowest_rank": link_min,
+                "link_frac": (d2h_per_step / (res_e["ms"] / args.steps * 1e-3) / 1e9) / link if link > 0 else None,
+                "link_probe": "1 s of pinned device-to-host copies of the same sizes, every rank at once, nothing else running"},
+        "roofline": {"bound": "issue", "kernel": "export_kernel (row carry + observation export + 32-ray sensor + fused shift)",
                      "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                     "traffic": NCU_TRAFFIC_BYTES_PER_AGENT_EXPORT * agents_per_launch,
-                     "traffic_source": "ncu --set full capture under profiles/ (bytes per agent x agents of this run)",
-                     "peak_source": peak_src,
-                     "algo_bytes_per_agent": ALGO_BYTES["export_sense"],
-                     "moved_bytes_per_agent": MOVED_BYTES_EXPORT,
-                     "achieved_moved": MOVED_BYTES_EXPORT * agents_per_launch / (k_ms * 1e-3) / 1e9 if k_ms > 0 else 0.0,
-                     "agents_per_launch": agents_per_launch, "kernel_ms": k_ms,
-                     "note": "issue-bound, not HBM-bound (32-ray sensor arithmetic): see issue_*",
-                     "issue_active_frac_ncu": NCU_EXPORT_ISSUE["issue_active_frac"],
-                     "issue_warp_instructions_per_world_ncu": NCU_EXPORT_ISSUE["warp_instructions_per_world"]},
-        "kernels": kernels,
+                     "traffic": traffic, "traffic_source": cap_src, "peak_source": peak_src,
+                     "algo_bytes_per_agent": algo_export,
+                     "algo_bytes_what": "236 B export share of STEP_BYTES (exports 44 W, sensors 64 W, prev-sensor carry 64 R + 64 W) "
+                                        "+ 264 B SHIFT_BYTES: the shift call is fused into this kernel (SURVEY.md 8(d))",
+                     "agents_per_launch": prof_agents, "kernel_ms": k_ms,
+                     "kernel_ms_source": "CUDA events between the kernels on the launch stream, K steps right after the timed region",
+                     "issue_frac": issue_frac, "issue_peak": "148 SMs x 4 schedulers x sampled SM clock (warp instructions / s)",
+                     "warp_instructions_per_world": inst_per_world,
+                     "note": "issue-bound (32-ray sensor arithmetic): frac is the algorithmic-HBM figure the contract asks for, "
+                             "issue_frac the fraction of the instruction-issue roofline"},
+        "kernels": kernels, "kernels_unfused_call_sequence": kernels_unfused,
         "episode_stats": dict(zip(("agent_steps", "steps", "births", "deaths", "respawns", "overflow"),
-                                  (tot[0], tot[1], tot[10], tot[11], tot[12], tot[13]))),
+                                  (res["stats"][0], res["stats"][1], res["stats"][10], res["stats"][11], res["stats"][12],
+                                   res["stats"][13]))),
     }
+    if weak:
+        line["weak_65536_per_gpu"] = weak
     if world == 1 and not args.no_cpu_baseline:
         line["cpu_baseline"] = cpu_baseline_sample()
     return line
@@ -464,6 +628,7 @@ def main():
                     help="fixed worlds per GPU instead (weak scaling); 0 = --worlds // --gpus")
     ap.add_argument("--ref-worlds", type=int, default=4096, help="worlds per step of the CPU reference arm")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-weak-leg", action="store_true", help="multi-GPU: skip the 65,536-worlds-per-GPU companion leg")
     ap.add_argument("--cap", type=int, default=0, help="per-world slot capacity (0 = library default, 128)")
     args = ap.parse_args()
     if args.warmup < 3:

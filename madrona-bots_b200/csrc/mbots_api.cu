@@ -74,7 +74,8 @@ struct mbots_sim {
     /* step graphs */
     bool useGraphs;
     cudaStream_t capStream;        /* capture happens here: the caller's stream may be the legacy default stream */
-    std::map<ChainKey, cudaGraphExec_t> graphs;
+    struct StepGraph { cudaGraphExec_t exec; int kernels; };
+    std::map<ChainKey, StepGraph> graphs;
     uint64_t graphLaunches;
 };
 
@@ -136,6 +137,7 @@ int alloc_all(mbots_sim *s)
     ALLOC(d.speciesCount, W); ALLOC(d.speciesReward, W); ALLOC(d.speciesHealth, W); ALLOC(d.wstats, W);
     ALLOC(d.sensorIndex, rows); ALLOC(d.done, rows); ALLOC(d.reset, W);
     ALLOC(d.totals, 1);
+    ALLOC(d.scanSync, 4);
     int rc = alloc_obs(s, d.obs[0], rows);
     if (rc != MBOTS_OK) return rc;
     rc = alloc_obs(s, d.obs[1], rows);
@@ -158,7 +160,7 @@ void free_all(mbots_sim *s)
     for (auto &e : s->ev) if (e) cudaEventDestroy(e);
     for (auto &e : s->evShift) if (e) cudaEventDestroy(e);
     if (s->evTotals) cudaEventDestroy(s->evTotals);
-    for (auto &kv : s->graphs) cudaGraphExecDestroy(kv.second);
+    for (auto &kv : s->graphs) cudaGraphExecDestroy(kv.second.exec);
     s->graphs.clear();
     if (s->capStream) cudaStreamDestroy(s->capStream);
 }
@@ -205,15 +207,15 @@ int finish(mbots_sim *s, cudaStream_t st)
 
 int enqueue_repack(mbots_sim *s, cudaStream_t st, int with_sensors, int count_step, uint32_t bound)
 {
-    launch_scan(s->d, s->cur, count_step, st);
+    const int nscan = launch_scan(s->d, s->cur, count_step, st);
     if (s->profile && with_sensors) cudaEventRecord(s->ev[2], st);
-    const int nexp = launch_export(s->d, s->cur, with_sensors, bound, st);
+    const int nexp = launch_export(s->d, s->cur, with_sensors, bound, nullptr, 0, 0, st);
     if (s->profile && with_sensors) cudaEventRecord(s->ev[3], st);
     CU(cudaGetLastError());
     CU(cudaMemcpyAsync(s->hTotals, s->d.totals, sizeof(Totals), cudaMemcpyDeviceToHost, st));
     CU(cudaEventRecord(s->evTotals, st));
     s->cur ^= 1;
-    s->launches += 2 + (uint64_t)nexp;                  /* tile sums, row scan, export variant(s) */
+    s->launches += (uint64_t)(nscan + nexp);            /* row scan (one or two kernels), export variant(s) */
     s->dirty = true;
     return MBOTS_OK;
 }
@@ -256,31 +258,25 @@ ChainKey chain_key(mbots_sim *s, const void *actions, unsigned long long action_
 /* the chain itself, on `st` (a real stream, or the capture stream). Returns the kernels launched. */
 int record_chain(mbots_sim *s, const ChainKey &k, cudaStream_t st, bool timing, bool external_event, int *launches)
 {
+    /* Fused rollout step: the step reads its actions straight from the caller's matrix and the export's carry writes them
+     * into the new rows (no action-write pass); with a shift requested the export leaves prev := cur (no shift pass). */
     int n = 0;
-    if (k.actions) { launch_action_write(s->d, k.cur, k.actions, k.actionRows, k.rowsUpper, st); n += 1; }
     if (timing) cudaEventRecord(s->ev[0], st);
-    launch_step(s->d, k.cur, k.stepSlots, st);
+    launch_step(s->d, k.cur, k.stepSlots, k.actions, k.actionRows, st);
     if (timing) cudaEventRecord(s->ev[1], st);
-    launch_scan(s->d, k.cur, 1, st);
+    n += 1 + launch_scan(s->d, k.cur, 1, st);
     if (timing) cudaEventRecord(s->ev[2], st);
-    n += 3 + launch_export(s->d, k.cur, 1, k.bound, st);
+    n += launch_export(s->d, k.cur, 1, k.bound, k.actions, k.actionRows, k.withShift, st);
     if (timing) cudaEventRecord(s->ev[3], st);
     CU(cudaGetLastError());
     CU(cudaMemcpyAsync(s->hTotals, s->d.totals, sizeof(Totals), cudaMemcpyDeviceToHost, st));
     if (external_event) CU(cudaEventRecordWithFlags(s->evTotals, st, cudaEventRecordExternal));
     else CU(cudaEventRecord(s->evTotals, st));
-    if (k.withShift) {
-        if (timing) cudaEventRecord(s->evShift[0], st);
-        launch_shift(s->d, k.cur ^ 1, k.rowsUpper, st);
-        if (timing) cudaEventRecord(s->evShift[1], st);
-        n += 1;
-        CU(cudaGetLastError());
-    }
     *launches = n;
     return MBOTS_OK;
 }
 
-int chain_launch_count(const ChainKey &k) { return 5 + (k.actions ? 1 : 0) + (k.withShift ? 1 : 0); }
+
 
 int enqueue_step(mbots_sim *s, cudaStream_t st, const void *actions = nullptr, unsigned long long action_rows = 0,
                  int with_shift = 0)
@@ -289,15 +285,15 @@ int enqueue_step(mbots_sim *s, cudaStream_t st, const void *actions = nullptr, u
     int n = 0;
     if (s->profile || !s->useGraphs) {
         /* per-kernel timing wants events between the kernels: plain stream launches */
-        if (s->profile) { resolve_step_timing(s); if (with_shift) resolve_shift_timing(s); }
+        if (s->profile) resolve_step_timing(s);
         int rc = record_chain(s, k, st, s->profile, false, &n);
         if (rc != MBOTS_OK) return rc;
-        if (s->profile) { s->stepPending = true; if (with_shift) s->shiftPending = true; }
+        if (s->profile) s->stepPending = true;
     } else {
         auto it = s->graphs.find(k);
         if (it == s->graphs.end()) {
             if (s->graphs.size() >= 256) {              /* geometry keeps changing: start over rather than grow */
-                for (auto &kv : s->graphs) cudaGraphExecDestroy(kv.second);
+                for (auto &kv : s->graphs) cudaGraphExecDestroy(kv.second.exec);
                 s->graphs.clear();
             }
             cudaGraph_t g = nullptr;
@@ -310,10 +306,10 @@ int enqueue_step(mbots_sim *s, cudaStream_t st, const void *actions = nullptr, u
             ce = cudaGraphInstantiate(&ex, g, 0);
             cudaGraphDestroy(g);
             if (ce != cudaSuccess) return fail(MBOTS_ECUDA, "cudaGraphInstantiate", ce);
-            it = s->graphs.emplace(k, ex).first;
+            it = s->graphs.emplace(k, mbots_sim::StepGraph{ex, n}).first;
         }
-        CU(cudaGraphLaunch(it->second, st));
-        n = chain_launch_count(k);
+        CU(cudaGraphLaunch(it->second.exec, st));
+        n = it->second.kernels;
         s->graphLaunches += 1;
     }
     s->cur ^= 1;
@@ -743,9 +739,10 @@ int mbots_load_state(mbots_sim *s, const void *host, uint64_t bytes, void *strea
     if (h.numWorlds != s->d.numWorlds || h.cap != s->d.cap || h.initAgents != s->d.initAgents)
         return fail(MBOTS_EINVAL, "checkpoint was taken with a different num_worlds / capacity / init agents");
     if ((uint64_t)h.totalAgents > (uint64_t)s->d.numWorlds * s->d.cap) return fail(MBOTS_EINVAL, "corrupt checkpoint");
+    if (s->dirty) return fail(MBOTS_ESTATE, "asynchronous work pending: call mbots_sync first");
     DeviceGuard g(s->device);
     cudaStream_t st = (cudaStream_t)stream;
-    CU(cudaStreamSynchronize(st));
+    CU(cudaDeviceSynchronize());                /* nothing on any stream (a caller's copy stream, a shift) may still touch the arrays */
     std::vector<Segment> segs;
     ckpt_segments(s, 0, h.totalAgents, segs);
     if (ckpt_total(segs) != h.bytes || bytes < h.bytes) return fail(MBOTS_EINVAL, "checkpoint size mismatch");
@@ -758,9 +755,26 @@ int mbots_load_state(mbots_sim *s, const void *host, uint64_t bytes, void *strea
     CU(cudaMemsetAsync(s->d.tileSum[0], 0, tiles * sizeof(TileSum), st));
     CU(cudaMemsetAsync(s->d.tileSum[1], 0, tiles * sizeof(TileSum), st));
     CU(cudaMemcpyAsync(s->d.totals, &h.totals, sizeof(Totals), cudaMemcpyHostToDevice, st));
+    /* a truncated or corrupt blob must not make the next step index out of bounds: check what the kernels trust */
+    launch_validate_state(s->d, h.totalAgents, reinterpret_cast<unsigned int *>(s->dStats), st);
+    CU(cudaMemcpyAsync(s->hStats, s->dStats, 2 * sizeof(unsigned int), cudaMemcpyDeviceToHost, st));
     CU(cudaStreamSynchronize(st));
+    {
+        const unsigned int *fl = reinterpret_cast<const unsigned int *>(s->hStats);
+        if (fl[0] != 0 || fl[1] != h.totalAgents || h.totals.totalAgents != h.totalAgents) {
+            /* leave the handle in a defined state: a fresh simulator of the same configuration */
+            launch_init(s->d, st);
+            s->cur = 0;
+            enqueue_repack(s, st, 0, 0, 0);
+            finish(s, st);
+            char msg[160];
+            snprintf(msg, sizeof msg, "corrupt checkpoint (flags %u, live agents %u vs header %u): handle re-initialised", fl[0], fl[1],
+                     h.totalAgents);
+            return fail(MBOTS_EINVAL, msg);
+        }
+    }
     s->d.worldIdOffset = h.worldIdOffset; s->d.seed = h.seed;
-    for (auto &kv : s->graphs) cudaGraphExecDestroy(kv.second);      /* the SimDev is baked into every kernel node */
+    for (auto &kv : s->graphs) cudaGraphExecDestroy(kv.second.exec);      /* the SimDev is baked into every kernel node */
     s->graphs.clear();
     s->cur = 0;
     *s->hTotals = h.totals;

@@ -74,6 +74,7 @@ struct SimDev {
     int32_t *done;            /* zeros (U10) */
     int32_t *reset;           /* zeros, ignored (U10) */
     Totals *totals;
+    unsigned int *scanSync;   /* two counters of scan_fused_kernel's grid barrier (zero between launches) */
 
     ObsSet obs[2];
 };
@@ -81,13 +82,15 @@ struct SimDev {
 /* launchers (sim_kernels.cu) */
 void prepare_kernels(const SimDev &d);
 void launch_init(const SimDev &d, cudaStream_t s);
-void launch_step(const SimDev &d, int cur, uint32_t slots, cudaStream_t s);
-void launch_scan(const SimDev &d, int cur, int count_step, cudaStream_t s);
-int launch_export(const SimDev &d, int cur, int with_sensors, uint32_t bound, cudaStream_t s);
+void launch_step(const SimDev &d, int cur, uint32_t slots, const void *act_src, unsigned long long act_rows, cudaStream_t s);
+int launch_scan(const SimDev &d, int cur, int count_step, cudaStream_t s);
+int launch_export(const SimDev &d, int cur, int with_sensors, uint32_t bound, const void *act_src, unsigned long long act_rows,
+                  int fuse_shift, cudaStream_t s);
 void launch_shift(const SimDev &d, int cur, uint32_t rows_upper, cudaStream_t s);
 void launch_action_write(const SimDev &d, int cur, const void *src, unsigned long long src_rows, uint32_t rows_upper, cudaStream_t s);
 void launch_stats_reduce(const SimDev &d, long long *out16, cudaStream_t s);
 void launch_debug_gather(const SimDev &d, int what, void *out, cudaStream_t s);
+void launch_validate_state(const SimDev &d, uint32_t total_agents, unsigned int *flags2, cudaStream_t s);
 /* launchers (policy_kernels.cu) */
 void launch_pack_obs(const ObsSet &o, int is_prev, uint32_t row_begin, uint32_t rows, float *out, cudaStream_t s);
 void launch_sample(const ObsSet &o, uint32_t row_begin, uint32_t rows, const float *weights, uint32_t seed, uint32_t draw,

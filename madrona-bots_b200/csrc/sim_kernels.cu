@@ -33,6 +33,24 @@ using namespace mbp;
 #define FULL 0xffffffffu
 
 /* ------------------------------------------------------------------------- */
+/* Options of a fused rollout step (mbots_rollout_step_async). actSrc: the caller's action matrix -- rows below
+ * actRows are read from it instead of the action export (the step takes its actions from there, the export's carry
+ * writes them into the new rows), so no separate action-write pass runs. fuseShift: the export kernel leaves the
+ * prev_* columns as shiftObservationsSystem + shiftHiddenState (src/sim/sim.cpp:1002-1048) would right after the
+ * step -- prev := cur, written in the same pass -- so no separate shift pass runs and the old prev rows are never read. */
+struct StepOpts {
+    const int2 *actSrc;
+    unsigned long long actRows;
+    int fuseShift;
+};
+
+__device__ __forceinline__ const int2 *action_row(const StepOpts &o, const int32_t *exported, int row)
+{
+    const bool ext = o.actSrc != nullptr && (unsigned long long)row < o.actRows;
+    return (ext ? o.actSrc : reinterpret_cast<const int2 *>(exported)) + (size_t)row * 3;
+}
+
+/* ------------------------------------------------------------------------- */
 /* small block-level helpers                                                   */
 
 __device__ __forceinline__ int comp(const int4 &v, int k)
@@ -131,7 +149,7 @@ __device__ __forceinline__ int warp_sum(int v) { return __reduce_add_sync(FULL, 
 #ifndef MBK_STEP_MIN_BLOCKS
 #define MBK_STEP_MIN_BLOCKS (32 / MBK_STEP_WARPS)
 #endif
-__global__ void __launch_bounds__(kStepWarps * 32, MBK_STEP_MIN_BLOCKS) step_kernel(SimDev d, int cur, uint32_t slots)
+__global__ void __launch_bounds__(kStepWarps * 32, MBK_STEP_MIN_BLOCKS) step_kernel(SimDev d, int cur, uint32_t slots, StepOpts opts)
 {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -186,11 +204,11 @@ __global__ void __launch_bounds__(kStepWarps * 32, MBK_STEP_MIN_BLOCKS) step_ker
         const int2 zero = make_int2(0, 0);
         int2 a0 = zero, a1 = zero, a2 = zero, b0 = zero, b1 = zero, b2 = zero;
         if (on_a) {
-            const int2 *ap = reinterpret_cast<const int2 *>(from.action + (size_t)row_a * 6);
+            const int2 *ap = action_row(opts, from.action, row_a);
             a0 = ap[0]; a1 = ap[1]; a2 = ap[2];
         }
         if (on_b) {
-            const int2 *bp = reinterpret_cast<const int2 *>(from.action + (size_t)row_b * 6);
+            const int2 *bp = action_row(opts, from.action, row_b);
             b0 = bp[0]; b1 = bp[1]; b2 = bp[2];
         }
         if (on_a) park(lane, pose_a, hp_a, sp_a, tgt_a, row_a, a0, a1, a2);
@@ -198,7 +216,7 @@ __global__ void __launch_bounds__(kStepWarps * 32, MBK_STEP_MIN_BLOCKS) step_ker
     }
     for (int s = 64 + lane; s < n0; s += 32) {
         const int row = d.row[base + s];
-        const int2 *ap = reinterpret_cast<const int2 *>(from.action + (size_t)row * 6);
+        const int2 *ap = action_row(opts, from.action, row);
         park(s, d.pose[base + s], d.health[base + s], d.species[base + s], d.target[base + s], row, ap[0], ap[1], ap[2]);
     }
     chunkAgents[lane] = 0;                              /* resetChunkInfoSystem (:390-396) */
@@ -543,6 +561,101 @@ __global__ void __launch_bounds__(kScanTile) scan_kernel(SimDev d, int cur, int 
     }
 }
 
+/* scan_fused_kernel: tile sums and row scan in ONE launch. Every CTA publishes the sums of its tile, then waits until
+ * all tiles have (a grid-wide barrier on a global counter: valid because the launcher only uses this kernel when every CTA
+ * of the grid is resident at once), then proceeds exactly as scan_kernel. The last CTA through resets the counters, so a
+ * captured graph can replay the launch with the same arguments. */
+__global__ void __launch_bounds__(kScanTile) scan_fused_kernel(SimDev d, int cur, int count_step, unsigned int *sync2)
+{
+    __shared__ int red[32][9];
+    __shared__ int fin[9];
+    __shared__ int wsum[32][5];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int W = (int)d.numWorlds, tile = blockIdx.x, nt = gridDim.x;
+    TileSum *ts = d.tileSum[cur];
+    const int w = tile * kScanTile + tid;
+    int4 c = make_int4(0, 0, 0, 0);
+    if (w < W) c = d.speciesLive[w];
+    int v[5] = {c.x, c.y, c.z, c.w, c.x + c.y + c.z + c.w};
+    int inc[5];
+#pragma unroll
+    for (int k = 0; k < 5; ++k) {
+        inc[k] = warp_incl_scan(v[k]);
+        if (lane == 31) wsum[warp][k] = inc[k];
+        const int mx = k == 4 ? __reduce_max_sync(FULL, v[k]) : 0;
+        if (lane == 0 && k == 4) red[warp][0] = mx;
+    }
+    __syncthreads();
+    if (tid < 5) {                                      /* this tile's sums (count of each species, largest world) */
+        int a = 0;
+        for (int i = 0; i < kScanTile / 32; ++i) a = tid == 4 ? max(a, red[i][0]) : a + wsum[i][tid];
+        if (tid == 4) ts[tile].maxCount = a; else ts[tile].c[tid] = a;
+    }
+    __syncthreads();
+    if (tid == 0) {
+        __threadfence();
+        atomicAdd(&sync2[0], 1u);
+        while (atomicAdd(&sync2[0], 0u) < (unsigned)nt) __nanosleep(64);
+        __threadfence();
+    }
+    __syncthreads();
+    int v9[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0};           /* totals[4], prefix of this tile[4], max count */
+    for (int t = tid; t < nt; t += kScanTile) {
+        /* written by other CTAs of this launch: read through L2, never from this SM's L1 */
+        const int4 xc = __ldcg(reinterpret_cast<const int4 *>(ts + t));
+        const int4 xm = __ldcg(reinterpret_cast<const int4 *>(ts + t) + 1);
+        const int xcv[4] = {xc.x, xc.y, xc.z, xc.w};
+#pragma unroll
+        for (int k = 0; k < 4; ++k) { v9[k] += xcv[k]; if (t < tile) v9[4 + k] += xcv[k]; }
+        v9[8] = max(v9[8], xm.x);
+    }
+#pragma unroll
+    for (int k = 0; k < 9; ++k) {
+        int u = v9[k];
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            const int y = __shfl_xor_sync(FULL, u, o);
+            u = k == 8 ? max(u, y) : u + y;
+        }
+        if (lane == 0) red[warp][k] = u;
+    }
+    __syncthreads();
+    if (tid < 9) {
+        int a = 0;
+        for (int i = 0; i < kScanTile / 32; ++i) a = tid == 8 ? max(a, red[i][tid]) : a + red[i][tid];
+        fin[tid] = a;
+    }
+    __syncthreads();
+    int base[5];
+    int spBase = 0, agentsBefore = 0;
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+        base[k] = spBase + fin[4 + k];
+        spBase += fin[k];
+        agentsBefore += fin[4 + k];
+    }
+    base[4] = agentsBefore;
+#pragma unroll
+    for (int k = 0; k < 5; ++k) {
+        int b = base[k];
+        for (int i = 0; i < warp; ++i) b += wsum[i][k];
+        base[k] = b + inc[k] - v[k];
+    }
+    if (w < W) {
+        d.rowBase[cur ^ 1][w] = make_int4(base[0], base[1], base[2], base[3]);
+        d.worldOffset[w] = base[4];
+    }
+    if (tid == 0) {
+        if (tile == 0) {
+            for (int k = 0; k < 4; ++k) d.totals->speciesTotal[k] = (uint32_t)fin[k];
+            d.totals->totalAgents = (uint32_t)spBase;
+            d.totals->maxWorldCount = (uint32_t)fin[8];
+            if (count_step) { d.totals->agentSteps += (unsigned long long)spBase; d.totals->steps += 1ull; }
+        }
+        if (atomicAdd(&sync2[1], 1u) == (unsigned)nt - 1u) { sync2[0] = 0u; sync2[1] = 0u; __threadfence(); }
+    }
+}
+
 /* ------------------------------------------------------------------------- */
 /* export_kernel: one WARP per world, kExportWarps independent worlds per CTA    */
 /* (one: worlds differ in population, and a CTA of four held its slot until    */
@@ -628,11 +741,16 @@ size_t export_smem_bytes(uint32_t slots, uint32_t tile, bool fast)
  * created this step (old row < 0) is zero-filled (DEVIATIONS.md D3). */
 template <typename V, int PARTS, int UNROLL>
 __device__ __forceinline__ void carry_column(void *dst, const void *src, const int *newrow, const int *oldrow,
-                                             int n, int lane)
+                                             int n, int lane, void *dst2 = nullptr, const void *ext = nullptr,
+                                             unsigned long long ext_rows = 0)
 {
+    /* dst2: a second column that receives the same rows (fused shift: prev := cur); ext: rows below ext_rows are read
+     * from this matrix instead of `src` (the caller's action matrix) */
     const int tasks = n * PARTS;
     V *dp = reinterpret_cast<V *>(dst);
+    V *dp2 = reinterpret_cast<V *>(dst2);
     const V *sp = reinterpret_cast<const V *>(src);
+    const V *ep = reinterpret_cast<const V *>(ext);
     for (int t0 = lane; t0 < tasks; t0 += 32 * UNROLL) {
         V v[UNROLL];
         size_t di[UNROLL];
@@ -645,12 +763,15 @@ __device__ __forceinline__ void carry_column(void *dst, const void *src, const i
                 const int a = t / PARTS, p = t - a * PARTS;
                 const int o = oldrow[a];
                 di[u] = (size_t)newrow[a] * PARTS + p;
-                if (o >= 0) v[u] = sp[(size_t)o * PARTS + p];
+                if (o >= 0) v[u] = (ep != nullptr && (unsigned long long)o < ext_rows ? ep : sp)[(size_t)o * PARTS + p];
             }
         }
 #pragma unroll
         for (int u = 0; u < UNROLL; ++u)
-            if (t0 + 32 * u < tasks) dp[di[u]] = v[u];
+            if (t0 + 32 * u < tasks) {
+                dp[di[u]] = v[u];
+                if (dp2 != nullptr) dp2[di[u]] = v[u];
+            }
     }
 }
 
@@ -661,7 +782,7 @@ __device__ __forceinline__ void carry_column(void *dst, const void *src, const i
  * `my` = this warp's shared memory (export_layout). */
 template <bool FAST>
 __device__ __forceinline__ void export_world(const SimDev &d, int cur, int with_sensors, uint32_t slots, uint32_t tile,
-                                             uint32_t w, int n, unsigned char *my, int split, int nsplit)
+                                             uint32_t w, int n, unsigned char *my, int split, int nsplit, const StepOpts &opts)
 {
     typedef Sense<FAST> S;
     typedef typename S::Key Key;
@@ -717,7 +838,7 @@ __device__ __forceinline__ void export_world(const SimDev &d, int cur, int with_
             int4 pst = make_int4(0, 0, 0, 0);
             float2 ppos = make_float2(0.f, 0.f), psur = make_float2(0.f, 0.f);
             float prew = 0.f, phl = 0.f;
-            if (old >= 0 && mine) {
+            if (old >= 0 && mine && !opts.fuseShift) {
                 pst = reinterpret_cast<const int4 *>(from.prev_stats)[old];
                 ppos = reinterpret_cast<const float2 *>(from.prev_position)[old];
                 psur = reinterpret_cast<const float2 *>(from.prev_surrounding)[old];
@@ -739,7 +860,15 @@ __device__ __forceinline__ void export_world(const SimDev &d, int cur, int with_
                 reinterpret_cast<float2 *>(to.surrounding)[row] = make_float2(sc.y, sc.z);
                 reinterpret_cast<int4 *>(to.stats)[row] = make_int4(st & 1u, (st >> 1) & 1u, (st >> 2) & 1u, (st >> 3) & 1u);
                 const float sterm = sp == 1 ? srew.x : sp == 2 ? srew.y : sp == 3 ? srew.z : srew.w;
-                to.reward[row] = with_sensors ? agent_reward(sterm, hp, (st & 4u) != 0, (st & 8u) != 0, (st & 2u) != 0) : 0.f;
+                const float rew = with_sensors ? agent_reward(sterm, hp, (st & 4u) != 0, (st & 8u) != 0, (st & 2u) != 0) : 0.f;
+                to.reward[row] = rew;
+                if (opts.fuseShift) {                   /* shiftObservationsSystem (:1018-1036) incl. the U7 field mix-up */
+                    pst = make_int4(st & 1u, st & 1u, (st >> 2) & 1u, (st >> 3) & 1u);
+                    ppos = make_float2(p.x, p.y);
+                    psur = make_float2(sc.y, sc.z);
+                    prew = rew;
+                    phl = (float)hp;
+                }
                 d.sensorIndex[off + s] = row;
                 d.row[base + s] = row;
                 if (!with_sensors) d.target[base + s] = (int16_t)-1;
@@ -756,10 +885,15 @@ __device__ __forceinline__ void export_world(const SimDev &d, int cur, int with_
     /* ---- the sort: the wide columns of the observation record follow their agent ---- */
     const int na = a_hi - a_lo;
     const int *nr = newrow + a_lo, *orow = oldrow + a_lo;
-    carry_column<float4, 4, 3>(to.hidden, from.hidden, nr, orow, na, lane);
-    carry_column<float4, 4, 3>(to.prev_hidden, from.prev_hidden, nr, orow, na, lane);
-    carry_column<int2, 3, 4>(to.action, from.action, nr, orow, na, lane);
-    carry_column<int2, 3, 4>(to.prev_action, from.prev_action, nr, orow, na, lane);
+    if (opts.fuseShift) {                               /* shiftHiddenState (:1039-1048), prev_action (:1025-1030): one read, two writes */
+        carry_column<float4, 4, 3>(to.hidden, from.hidden, nr, orow, na, lane, to.prev_hidden);
+        carry_column<int2, 3, 4>(to.action, from.action, nr, orow, na, lane, to.prev_action, opts.actSrc, opts.actRows);
+    } else {
+        carry_column<float4, 4, 3>(to.hidden, from.hidden, nr, orow, na, lane);
+        carry_column<float4, 4, 3>(to.prev_hidden, from.prev_hidden, nr, orow, na, lane);
+        carry_column<int2, 3, 4>(to.action, from.action, nr, orow, na, lane, nullptr, opts.actSrc, opts.actRows);
+        carry_column<int2, 3, 4>(to.prev_action, from.prev_action, nr, orow, na, lane);
+    }
     /* updateSensorOutputIdx (:774-780): last frame's sensor rows become the prev rows */
     carry_column<int4, 2, 3>(to.prev_semantic, from.semantic, nr, orow, na, lane);
     carry_column<int4, 2, 3>(to.prev_depth, from.depth, nr, orow, na, lane);
@@ -938,7 +1072,7 @@ __device__ __forceinline__ void export_world(const SimDev &d, int cur, int with_
  *               worlds with a small grid, and nothing at all when no world is that large). */
 template <bool FAST>
 __global__ void __launch_bounds__(kExportWarps * 32, FAST ? kExportFastMinBlocks : 16 / kExportWarps)
-export_kernel(SimDev d, int cur, int with_sensors, uint32_t slots, uint32_t tile, int skip_upto, int split_log2)
+export_kernel(SimDev d, int cur, int with_sensors, uint32_t slots, uint32_t tile, int skip_upto, int split_log2, StepOpts opts)
 {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     const int warp = threadIdx.x >> 5;
@@ -950,12 +1084,12 @@ export_kernel(SimDev d, int cur, int with_sensors, uint32_t slots, uint32_t tile
         if (w >= d.numWorlds) return;               /* whole warp: no block-level barrier anywhere */
         const int n = d.worldCount[w];
         if (n > (int)slots || n > 63) return;       /* slot 63 is the miss sentinel of the 32-bit keys */
-        export_world<FAST>(d, cur, with_sensors, slots, tile, w, n, my, (int)(unit & ((1u << split_log2) - 1u)), 1 << split_log2);
+        export_world<FAST>(d, cur, with_sensors, slots, tile, w, n, my, (int)(unit & ((1u << split_log2) - 1u)), 1 << split_log2, opts);
     } else {
         for (uint32_t w = blockIdx.x * kExportWarps + warp; w < d.numWorlds; w += gridDim.x * kExportWarps) {
             const int n = d.worldCount[w];
             if (n <= skip_upto) continue;
-            export_world<FAST>(d, cur, with_sensors, slots, tile, w, n, my, 0, 1);
+            export_world<FAST>(d, cur, with_sensors, slots, tile, w, n, my, 0, 1, opts);
             __syncwarp();
         }
     }
@@ -1137,29 +1271,47 @@ void prepare_kernels(const SimDev &d)
     }
 }
 
-void launch_step(const SimDev &d, int cur, uint32_t slots, cudaStream_t s)
+static StepOpts make_opts(const void *act_src, unsigned long long act_rows, int fuse_shift)
+{
+    StepOpts o;
+    o.actSrc = reinterpret_cast<const int2 *>(act_src);
+    o.actRows = act_src ? act_rows : 0ull;
+    o.fuseShift = fuse_shift;
+    return o;
+}
+
+void launch_step(const SimDev &d, int cur, uint32_t slots, const void *act_src, unsigned long long act_rows, cudaStream_t s)
 {
     /* slots: a bound on the live agents of any world before the step; the capacity always is one */
     if (slots == 0 || slots > d.cap) slots = d.cap;
     const size_t smem = step_smem_bytes(slots);
-    step_kernel<<<(d.numWorlds + kStepWarps - 1) / kStepWarps, kStepWarps * 32, smem, s>>>(d, cur, slots);
+    step_kernel<<<(d.numWorlds + kStepWarps - 1) / kStepWarps, kStepWarps * 32, smem, s>>>(d, cur, slots, make_opts(act_src, act_rows, 0));
 }
 
-void launch_scan(const SimDev &d, int cur, int count_step, cudaStream_t s)
+/* Returns the kernels launched: one (scan_fused_kernel) while every tile's CTA fits on the GPU at once -- its grid-wide
+ * barrier needs that; 148 SMs x one 1,024-thread CTA = 151,552 worlds -- otherwise tile sums and row scan as two. */
+int launch_scan(const SimDev &d, int cur, int count_step, cudaStream_t s)
 {
     const unsigned tiles = (d.numWorlds + kScanTile - 1) / kScanTile;
+    static int fused = -1;
+    if (fused < 0) { const char *e = getenv("MBOTS_SCAN_FUSED"); fused = !(e && e[0] == '0'); }
+    if (fused && tiles <= 148u && d.scanSync != nullptr) {
+        scan_fused_kernel<<<tiles, kScanTile, 0, s>>>(d, cur, count_step, d.scanSync);
+        return 1;
+    }
     tile_sum_kernel<<<tiles, kScanTile, 0, s>>>(d, cur);
     scan_kernel<<<tiles, kScanTile, 0, s>>>(d, cur, count_step);
+    return 2;
 }
 
 template <bool FAST>
 static void launch_export_variant(const SimDev &d, int cur, int with_sensors, uint32_t slots, uint32_t tile, int skip_upto,
-                                  int split_log2, cudaStream_t s)
+                                  int split_log2, const StepOpts &opts, cudaStream_t s)
 {
     const size_t smem = export_smem_bytes(slots, tile, FAST);
     uint32_t grid = ((d.numWorlds << split_log2) + kExportWarps - 1) / kExportWarps;
     if (!FAST && skip_upto >= 0 && grid > 148u * 4u) grid = 148u * 4u;   /* clean-up pass: few worlds, if any */
-    export_kernel<FAST><<<grid, kExportWarps * 32, smem, s>>>(d, cur, with_sensors, slots, tile, skip_upto, split_log2);
+    export_kernel<FAST><<<grid, kExportWarps * 32, smem, s>>>(d, cur, with_sensors, slots, tile, skip_upto, split_log2, opts);
 }
 
 /* Parts per world of the FAST export kernel (log2): a full GPU wants ~32 resident single-warp CTAs per SM; below that a
@@ -1180,19 +1332,21 @@ static int export_split_log2(uint32_t numWorlds)
 
 /* bound: the largest world the caller expects after this step (0 = unknown). Worlds above it are still
  * handled -- by the full kernel -- so a wrong bound costs time, never correctness. Returns the launches made. */
-int launch_export(const SimDev &d, int cur, int with_sensors, uint32_t bound, cudaStream_t s)
+int launch_export(const SimDev &d, int cur, int with_sensors, uint32_t bound, const void *act_src, unsigned long long act_rows,
+                  int fuse_shift, cudaStream_t s)
 {
+    const StepOpts opts = make_opts(act_src, act_rows, fuse_shift);
     uint32_t fast_slots = (bound + 7u) & ~7u;
     if (bound == 0 || fast_slots > (uint32_t)kFastSlots || fast_slots > d.cap) {
-        launch_export_variant<false>(d, cur, with_sensors, d.cap, kFullTile, -1, 0, s);
+        launch_export_variant<false>(d, cur, with_sensors, d.cap, kFullTile, -1, 0, opts, s);
         return 1;
     }
     /* 32 observers per sensor tile: 56 slots + 4 KB of keys = 6.1 KB per single-warp CTA, 32 of them per SM.
      * (One tile for the whole world -- 40 observers, 26-28 CTAs per SM -- measured 1 % slower.) */
     uint32_t tile = (uint32_t)MBK_EXPORT_FAST_TILE;
     if (tile > fast_slots) tile = fast_slots;
-    launch_export_variant<true>(d, cur, with_sensors, fast_slots, tile, 0, export_split_log2(d.numWorlds), s);
-    launch_export_variant<false>(d, cur, with_sensors, d.cap, kFullTile, (int)(fast_slots < 63u ? fast_slots : 63u), 0, s);
+    launch_export_variant<true>(d, cur, with_sensors, fast_slots, tile, 0, export_split_log2(d.numWorlds), opts, s);
+    launch_export_variant<false>(d, cur, with_sensors, d.cap, kFullTile, (int)(fast_slots < 63u ? fast_slots : 63u), 0, opts, s);
     return 2;
 }
 
@@ -1212,6 +1366,29 @@ void launch_stats_reduce(const SimDev &d, long long *out16, cudaStream_t s)
     unsigned blocks = (d.numWorlds + 255) / 256;
     if (blocks > 148u * 4u) blocks = 148u * 4u;
     stats_reduce_kernel<<<blocks, 256, 0, s>>>(d, out16);
+}
+
+/* Consistency of a restored state (mbots_load_state): flags[0] |= 1 a world count above the capacity, 2 a row outside
+ * [0, totalAgents), 4 a finder target outside [-1, count), 8 a species outside 1..4; flags[1] += live agents. */
+__global__ void validate_state_kernel(SimDev d, uint32_t total_agents, unsigned int *flags)
+{
+    const uint32_t w = blockIdx.x;
+    const int n = d.worldCount[w];
+    if (n < 0 || n > (int)d.cap) { if (threadIdx.x == 0) atomicOr(&flags[0], 1u); return; }
+    if (threadIdx.x == 0) atomicAdd(&flags[1], (unsigned)n);
+    const size_t base = (size_t)w * d.cap;
+    for (int s = threadIdx.x; s < n; s += blockDim.x) {
+        const int row = d.row[base + s], tgt = d.target[base + s], sp = d.species[base + s];
+        if (row < 0 || (uint32_t)row >= total_agents) atomicOr(&flags[0], 2u);
+        if (tgt < -1 || tgt >= n) atomicOr(&flags[0], 4u);
+        if (sp < 1 || sp > kNumSpecies) atomicOr(&flags[0], 8u);
+    }
+}
+
+void launch_validate_state(const SimDev &d, uint32_t total_agents, unsigned int *flags2, cudaStream_t s)
+{
+    cudaMemsetAsync(flags2, 0, 2 * sizeof(unsigned int), s);
+    validate_state_kernel<<<d.numWorlds, 64, 0, s>>>(d, total_agents, flags2);
 }
 
 void launch_debug_gather(const SimDev &d, int what, void *out, cudaStream_t s)

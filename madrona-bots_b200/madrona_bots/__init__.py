@@ -73,6 +73,9 @@ class Tensor:
                                               None), device=dev)
                 cache[key] = base
             t = base[: self._shape[0]]
+            # the view handed out keeps the simulator (and so the device memory behind the pointer) alive; the cached
+            # base does not, or the handle would sit in a reference cycle and be destroyed only by the cycle collector
+            t._mbots_owner = self._owner
         assert t.data_ptr() == self._ptr, "expected a zero-copy view"
         return t
 

@@ -22,7 +22,7 @@ left untouched. Parity for this part is against torch's own modules (tests/test_
 import glob
 import os
 
-__all__ = ["SpeciesPolicy", "FusedPolicy", "PolicyRunner", "load_universe"]
+__all__ = ["SpeciesPolicy", "FusedPolicy", "PolicyRunner", "load_universe", "load_universe_fixture"]
 
 _ACTIVATIONS = ("Tanh", "ELU", "LogSigmoid", "LeakyReLU", "ReLU")     # learn/models.py:63-69
 
@@ -274,6 +274,22 @@ def load_universe(base_dir, device, metric="latest", num_species=4, dtype="fp32"
             raise FileNotFoundError(f"no {pat} under {base_dir}/species_{k}")
         files.sort(key=lambda p: int(p.split("_")[-1].split(".")[0]), reverse=True)
         out.append(SpeciesPolicy.from_checkpoint(files[0], device, dtype))
+    return out
+
+
+def load_universe_fixture(npz_path, device, dtype="fp32", num_species=4):
+    """The four species networks of checkpoints/universe_violence from the fixture tests/golden/make_policy_golden.py
+    writes (weights + model_config per species, fp32): what a box without /root/reference loads instead."""
+    import json
+    import numpy as np
+    import torch
+    z = np.load(npz_path)
+    out = []
+    for k in range(1, num_species + 1):
+        cfg = json.loads(bytes(z[f"sp{k}.config_json"]).decode())
+        pre = f"sp{k}.w."
+        sd = {n[len(pre):]: torch.from_numpy(z[n]) for n in z.files if n.startswith(pre)}
+        out.append(SpeciesPolicy(cfg, sd, device, dtype))
     return out
 
 

@@ -7,15 +7,23 @@
  * call it. Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline /
  * --impl reference legs use it.
  *
- * Parity status: the reference has no CPU backend and does not compile at its
- * pinned submodule commit, and its tests hold no golden
- * vectors for the step. What IS pinned: the RNG and quaternion arithmetic, by
- * building this same file against the reference's own rand.hpp / math.hpp
- * (-DMBO_REF_PRIMS -> oracle/_ref/) and requiring bit-identical trajectories,
- * and by the known-answer tests of M/tests/rand.cpp:131-141 and
- * M/tests/math.cpp:23-48. The step semantics themselves are "parity unpinned":
- * they follow the source lines cited at each function and the canonical
- * ordering rules of SURVEY.md section 8a (U3-U19), listed in DEVIATIONS.md.
+ * Parity status: PINNED to the reference's own source text. The reference has no CPU backend and
+ * does not compile at its pinned submodule commit, and its tests hold no
+ * golden vectors for the step -- but its system bodies are plain C++ once an `Engine` exists:
+ * oracle/refmock/ compiles src/sim/sim.cpp, external/madrona/src/render/ecs_system.cpp and
+ * raySphereIntersect / traceRayTLAS / bvhRaycastEntry of external/madrona/src/mw/device/
+ * bvh_raycast.cpp FROM WHERE THEY LIE (`make -C oracle refsim` -> oracle/_ref/librefsim.so) and
+ * runs one world through the reference's own task graphs under a host mock of the ECS runtime.
+ * tests/test_reference_bodies.py requires every export of this oracle to equal that world's, bit
+ * for bit, at every step (positions, rotations, health, food, RNG stream, rewards, surroundings,
+ * statistics, 32-ray depth rows, finder targets, prev columns), under the rules U5, U6, U8, U19,
+ * D2, D3 of DEVIATIONS.md -- each switchable, with the literal text's differential tested too.
+ * tests/golden/refsim_rollouts.npz holds digests of such worlds for boxes without /root/reference.
+ * Also pinned: the RNG and quaternion arithmetic, by building this same file against the
+ * reference's own rand.hpp / math.hpp (-DMBO_REF_PRIMS -> oracle/_ref/) with bit-identical
+ * trajectories, and the known answers of M/tests/rand.cpp:131-141 and M/tests/math.cpp:23-48.
+ * Still unpinned: the semantic sensor channel (no source for it exists at the pinned commit) and
+ * the cross-world row order (global atomics in the reference; canonical rule U11 here).
  *
  * One world is advanced by one thread; worlds are independent, so a small
  * std::thread pool parallelises over worlds (no OpenMP runtime dependency). All arithmetic is IEEE single precision, compiled

@@ -116,3 +116,32 @@ def test_trajectory_dump_matches_oracle(cuda_device, tmp_path):
         for k, v in e.items():
             np.testing.assert_array_equal(z[k][so[t]:so[t + 1]], v, err_msg=f"step {t}: {k}")
     assert set(np.unique(z["world"])) == set(worlds)
+
+
+def test_corrupt_checkpoint_is_rejected(cuda_device):
+    """A blob whose world counts / rows / targets are out of range must not reach the kernels: load_state
+    answers MBOTS_EINVAL and leaves a usable, re-initialised handle."""
+    from madrona_bots import SimManager
+    W, cap = 8, 128
+    g = SimManager(0, W, 5, 32)
+    for _ in range(3):
+        g.step()
+    blob = g.save_state()
+    slots = W * cap
+    off_count = 80 + slots * (16 + 4 + 1 + 2 + 16 + 4)          # header, pose, health, species, target, scratch, row
+    assert np.frombuffer(blob[off_count:off_count + 4 * W].tobytes(), dtype=np.int32).tolist() == \
+        gpu_np(g, "DEBUG_WORLD_COUNT")[:, 0].tolist()
+    bad = blob.copy()
+    bad[off_count:off_count + 4] = np.frombuffer(np.int32(100000).tobytes(), dtype=np.uint8)
+    h = SimManager(0, W, 9, 32)
+    with pytest.raises(RuntimeError, match="corrupt checkpoint"):
+        h.load_state(bad)
+    h.step()                                                      # still a working simulator
+    assert h.num_agents() >= W * 32
+    bad2 = blob.copy()
+    off_row = 80 + slots * (16 + 4 + 1 + 2 + 16)
+    bad2[off_row:off_row + 4] = np.frombuffer(np.int32(-7).tobytes(), dtype=np.uint8)
+    with pytest.raises(RuntimeError, match="corrupt checkpoint"):
+        h.load_state(bad2)
+    h.load_state(blob)                                            # and the intact blob still restores
+    np.testing.assert_array_equal(gpu_np(h, "DEBUG_POSE"), gpu_np(g, "DEBUG_POSE"))

@@ -341,7 +341,8 @@ def test_rollout_step_graph_and_run_ahead_match_oracle(cuda_device, worlds, dept
         g.sync()
         torch.cuda.synchronize()
         compare(o, g, f"graph step {t} (depth {depth})")
-    assert g.graph_launch_count() == t
+    import os
+    assert g.graph_launch_count() == (0 if os.environ.get("MBOTS_GRAPHS") == "0" else t)
     st = o.episode_stats()
     assert st[10] > 0 and st[11] > 0
 

@@ -70,3 +70,26 @@ def test_unknown_layers_are_rejected():
     bad = dict(config, recurrent={"type": "Transformer", "input_dim": 128, "hidden_dim": 128})
     with pytest.raises(ValueError):
         SpeciesPolicy(bad, net.state_dict(), "cpu")
+
+
+def test_species_policy_equals_reference_models_py_on_shipped_weights():
+    """tests/golden/policy_universe_violence.npz: logits and values of the reference's OWN learn/models.py
+    (ActorCritic.forward, one agent at a time = one recurrent step from a zero state, DEVIATIONS.md D4) on the shipped
+    checkpoints/universe_violence weights, 512 fixed observation rows. The host-side evaluation must agree in fp32."""
+    import numpy as np
+    from madrona_bots.policy import load_universe_fixture
+    path = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "policy_universe_violence.npz")
+    z = np.load(path)
+    obs = torch.from_numpy(np.concatenate([z["depth"].astype(np.float32), z["health"], z["position"],
+                                           z["semantic"].astype(np.float32), z["surrounding"]], axis=1))
+    pols = load_universe_fixture(path, "cpu")
+    kinds = [p.rtype for p in pols]
+    assert kinds == ["GRU", "LSTM", "RNN", "RNN"], kinds            # SURVEY.md C20
+    for k, pol in enumerate(pols, 1):
+        logits, value = pol.forward(obs)
+        ref_l, ref_v = torch.from_numpy(z[f"sp{k}.logits"]), torch.from_numpy(z[f"sp{k}.values"])
+        scale = float(ref_l.abs().max())
+        assert float((logits - ref_l).abs().max()) <= 2e-5 * scale, (k, float((logits - ref_l).abs().max()), scale)
+        assert float((value - ref_v).abs().max()) <= 2e-5 * float(ref_v.abs().max()) + 1e-4
+        # the reference's loop feeds all agents as ONE sequence (learn/models.py:163-167): its row 0 is the zero-state step
+        np.testing.assert_allclose(z[f"sp{k}.logits_as_one_sequence_row0"], z[f"sp{k}.logits"][0], rtol=1e-5, atol=1e-3)
