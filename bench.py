@@ -370,6 +370,63 @@ def link_probe(dev, sizes, seconds=1.0):
     return sum(sizes) * reps / (e0.elapsed_time(e1) * 1e-3) / 1e9
 
 
+def policy_leg(args, sim, leg, dev, world, idx):
+    """learn/training_loop.py:36-83,135-137 without the learner: step(), then per species ONE fused acting kernel
+    (construct_obs -> species network on tcgen05 tensor cores -> softmax -> Categorical sample -> one-hot action rows,
+    csrc/policy_umma.cu), then shift_observations(). Weights: the shipped checkpoints/universe_violence networks
+    (fixture tests/golden/policy_universe_violence.npz, written by make_policy_golden.py from the reference's files)."""
+    import torch
+    from madrona_bots.policy import PolicyRunner, load_universe_fixture
+    from madrona_bots.sharding import allreduce_max, allreduce_stats
+    path = os.path.join(ROOT, "tests", "golden", "policy_universe_violence.npz")
+    pols = load_universe_fixture(path, dev)
+    runner = PolicyRunner(sim, pols, seed=SEED, fused="sw128")
+    flops_per_agent = []
+    for p in pols:                                    # useful multiply-adds of one agent's forward pass (actor path)
+        macs = sum(l[1].shape[0] * l[1].shape[1] for l in p.feature if l[0] == "linear")
+        macs += p.w_ih_t.shape[0] * (p.hidden_dim * (3 if p.rtype in ("GRU", "LSTM") else 1))   # LSTM: f gate unused from c0 = 0
+        macs += sum(l[1].shape[0] * l[1].shape[1] for l in p.actor if l[0] == "linear")
+        flops_per_agent.append(2.0 * macs)
+    ev = [torch.cuda.Event(enable_timing=True) for _ in range(4)]
+    t_pol = t_all = 0.0
+    flops = 0.0
+    agent_steps = 0
+    for t in range(args.warmup + args.steps):
+        ev[0].record()
+        sim.step()
+        ev[1].record()
+        blocks = sim.species_blocks()
+        runner.act()
+        ev[2].record()
+        sim.shift_observations_async()
+        ev[3].record()
+        torch.cuda.synchronize()
+        if t >= args.warmup:
+            t_pol += ev[1].elapsed_time(ev[2])
+            t_all += ev[0].elapsed_time(ev[3])
+            agent_steps += sim.num_agents()
+            flops += sum(f * (b - a) for f, (a, b) in zip(flops_per_agent, blocks))
+    tot = allreduce_stats([agent_steps, 0, int(flops / 1e6)], device=dev)
+    t_all_max = allreduce_max(t_all, device=dev)
+    t_pol_max = allreduce_max(t_pol, device=dev)
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            tf_peak, tf_src = float(json.load(f)["bf16_tflops_sustained"]), "MEASURED_PEAKS.json bf16_tflops_sustained"
+    except Exception:
+        tf_peak, tf_src = 1400.0, "fallback"
+    tflops = tot[2] * 1e6 / (t_pol_max * 1e-3) / 1e12 / world          # per GPU
+    return {"value": tot[0] / (t_all_max * 1e-3), "unit": UNIT, "ms_per_step": t_all_max / args.steps,
+            "policy_ms_per_step": t_pol_max / args.steps, "steps": args.steps,
+            "what": "step() + 4 fused acting kernels (tcgen05, bf16 in / fp32 accumulate) + shift_observations per step; "
+                    "the host waits for every step (the species row ranges come from it)",
+            "weights": "checkpoints/universe_violence latest_model_epoch_788 (GRU, LSTM, RNN, RNN), fixture npz",
+            "roofline": {"bound": "tensor", "kernel": "policy_umma_kernel (4 launches per step, one per species)",
+                         "achieved": tflops, "peak": tf_peak, "unit": "TFLOP/s", "frac": tflops / tf_peak, "peak_source": tf_src,
+                         "flops_per_agent": flops_per_agent,
+                         "note": "useful FLOPs of the networks (no padding); the time includes the four launches and the "
+                                 "host's species_blocks() read between them"}}
+
+
 RUN_AHEAD = 3          # steps the host may have in flight in the device-resident leg
 
 
@@ -510,8 +567,13 @@ def run_ours(args, rank, world, local_rank):
     d2h_per_step = moved["d2h"] // max(1, e2e_steps)
     leg.barrier()
     link = link_probe(dev, [prof_agents * b for _, b in obs_names] + [W * 16], seconds=1.0)
-    link_all = allreduce_stats([int(link * 1e6)], device=dev)[0] / 1e6 if world > 1 else link
+    link_all = allreduce_stats([int(link * 1e6), 0], device=dev)[0] / 1e6 if world > 1 else link
     link_min = -allreduce_max(-link, device=dev) if world > 1 else link
+
+    # ---------------- policy in the loop (BASELINE.json configs[4]: universe_violence policy, inference part) ----------------
+    policy = None
+    if args.policy:
+        policy = policy_leg(args, sim, leg, dev, world, idx)
 
     # ---------------- weak-scaling companion: 65,536 worlds on every GPU ----------------
     weak = None
@@ -611,6 +673,8 @@ def run_ours(args, rank, world, local_rank):
     }
     if weak:
         line["weak_65536_per_gpu"] = weak
+    if policy:
+        line["policy_rollout"] = policy
     if world == 1 and not args.no_cpu_baseline:
         line["cpu_baseline"] = cpu_baseline_sample()
     return line
@@ -629,6 +693,8 @@ def main():
     ap.add_argument("--ref-worlds", type=int, default=4096, help="worlds per step of the CPU reference arm")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-weak-leg", action="store_true", help="multi-GPU: skip the 65,536-worlds-per-GPU companion leg")
+    ap.add_argument("--policy", action="store_true",
+                    help="add the policy-in-the-loop leg (universe_violence networks through the fused tcgen05 acting kernel)")
     ap.add_argument("--cap", type=int, default=0, help="per-world slot capacity (0 = library default, 128)")
     args = ap.parse_args()
     if args.warmup < 3:

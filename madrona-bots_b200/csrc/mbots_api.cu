@@ -239,7 +239,7 @@ ChainKey chain_key(mbots_sim *s, const void *actions, unsigned long long action_
     if (need < 32u) need = 32u;
     uint32_t rows = s->hTotals->totalAgents;
     if (s->dirty) {
-        need += 8u;
+        need += 3u;                                     /* the largest world moves by a few agents per step; keep 32 CTAs per SM */
         rows += rows / 4u + 1024u;
     }
     const uint64_t cap_rows = (uint64_t)s->d.numWorlds * s->d.cap;

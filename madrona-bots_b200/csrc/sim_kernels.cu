@@ -32,6 +32,16 @@ using namespace mbp;
 
 #define FULL 0xffffffffu
 
+/* -DMBK_CHECKED (lib/variants/libmbots_checked.so, `make checked`): every shared-memory and row index the kernels form is
+ * asserted in range (device assert -> the next CUDA call fails). Stands in for compute-sanitizer's memcheck, which is
+ * closed on this GPU pool; the parity suite is run once against this build (tools/gpu_checked.sh). */
+#if defined(MBK_CHECKED)
+#include <assert.h>
+#define MBK_CHECK(cond) assert(cond)
+#else
+#define MBK_CHECK(cond) ((void)0)
+#endif
+
 /* ------------------------------------------------------------------------- */
 /* Options of a fused rollout step (mbots_rollout_step_async). actSrc: the caller's action matrix -- rows below
  * actRows are read from it instead of the action export (the step takes its actions from there, the export's carry
@@ -183,6 +193,7 @@ __global__ void __launch_bounds__(kStepWarps * 32, MBK_STEP_MIN_BLOCKS) step_ker
     int tgt_a = d.target[ia], tgt_b = d.target[ib];
     int row_a = d.row[ia], row_b = d.row[ib];
     const int n0 = d.worldCount[w];
+    MBK_CHECK(n0 >= 0 && (uint32_t)n0 <= slots && slots <= cap);
     const uint2 kk = d.rngKey[w];
     const uint32_t rng0 = d.rngCount[w];
     int numFood = d.numFood[w];
@@ -193,6 +204,8 @@ __global__ void __launch_bounds__(kStepWarps * 32, MBK_STEP_MIN_BLOCKS) step_ker
                     const int2 &a2) {
         const uint32_t act = (a0.x != 0) | ((a0.y != 0) << 1) | ((a1.x != 0) << 2) | ((a1.y != 0) << 3) |
                              ((a2.x != 0) << 4) | ((a2.y != 0) << 5);
+        MBK_CHECK(s >= 0 && (uint32_t)s < slots && sp >= 1u && sp <= 4u && tgt >= -1 && tgt < n0);
+        MBK_CHECK(row >= 0 && (uint32_t)row < d.numWorlds * d.cap);
         spose[s] = pose;
         accum[s] = hp;
         soldrow[s] = row;
@@ -286,6 +299,7 @@ __global__ void __launch_bounds__(kStepWarps * 32, MBK_STEP_MIN_BLOCKS) step_ker
         const float len = move_agent(pose.x, pose.y, rot, (info & 1u) != 0, (info & 2u) != 0, (info & 4u) != 0, (info & 8u) != 0);
         pose.z = rot.w; pose.w = rot.z;
         const int c = chunk_of(pose.x, pose.y);
+        MBK_CHECK(c >= 0 && c < kNumChunks);
         atomicAdd(&chunkAgents[c], 1u);
         atomicAdd(&chunkSpeed[c], (uint32_t)(len * 2.f));
         spose[s] = pose;
@@ -353,12 +367,14 @@ __global__ void __launch_bounds__(kStepWarps * 32, MBK_STEP_MIN_BLOCKS) step_ker
         __syncwarp();                                   /* every lane has read its parked record */
         if (live) {
             const size_t o = base + (size_t)lidx;
+            MBK_CHECK(lidx >= 0 && (uint32_t)lidx < cap && mychunk >= 0 && mychunk < kNumChunks);
             d.pose[o] = pose;
             d.health[o] = hp;
             d.species[o] = (uint8_t)sp;
             d.scratch[o] = make_float4(__int_as_float(oldrow), sn, ss, __int_as_float((int)stat));
         }
         if (childOk) {                                  /* park the newborn: its slot needs the final live count */
+            MBK_CHECK(bidx >= 0 && (uint32_t)bidx < slots);
             spose[bidx] = make_float4(pose.x, pose.y, sn, ss);
             sinfo[bidx] = (uint32_t)sp;
         }
@@ -370,6 +386,7 @@ __global__ void __launch_bounds__(kStepWarps * 32, MBK_STEP_MIN_BLOCKS) step_ker
     for (int b = lane; b < bornOk; b += 32) {           /* a newborn shares its parent's position and surroundings */
         const float4 c = spose[b];
         const size_t o = base + (size_t)(nLive + b);
+        MBK_CHECK((uint32_t)(nLive + b) < cap);
         d.pose[o] = make_float4(c.x, c.y, 1.f, 0.f);
         d.health[o] = 50;
         d.species[o] = (uint8_t)sinfo[b];
@@ -397,6 +414,7 @@ __global__ void __launch_bounds__(kStepWarps * 32, MBK_STEP_MIN_BLOCKS) step_ker
         const float y = key_sample_uniform(key_split(wkey, rngBase + 2u * s + 1u)) * kWorldY;
         if (s < respOk) {
             const size_t o = base + (size_t)(nLive + bornOk) + s;
+            MBK_CHECK((uint32_t)(nLive + bornOk) + s < cap);
             d.pose[o] = make_float4(x, y, 1.f, 0.f);
             d.health[o] = 100;
             d.species[o] = (uint8_t)(k + 1);
@@ -834,6 +852,8 @@ __device__ __forceinline__ void export_world(const SimDev &d, int cur, int with_
             const int row = comp(rb, sp - 1) + rank;
             const int old = __float_as_int(sc.x);
             const bool mine = s >= a_lo && s < a_hi;
+            MBK_CHECK((uint32_t)s < slots && sp >= 1 && sp <= 4 && row >= 0 && (uint32_t)row < d.numWorlds * d.cap);
+            MBK_CHECK(old >= -1 && (old < 0 || (uint32_t)old < d.numWorlds * d.cap));
             /* carried small columns: issue the loads first */
             int4 pst = make_int4(0, 0, 0, 0);
             float2 ppos = make_float2(0.f, 0.f), psur = make_float2(0.f, 0.f);
@@ -927,8 +947,11 @@ __device__ __forceinline__ void export_world(const SimDev &d, int cur, int with_
             const float2 qi = pos[tile0 + ol], qj = pos[j];
             const Ray ray = make_ray(theta[tile0 + ol], r);
             float t;
-            if (ray_sphere(ray, qi.x - qj.x, qi.y - qj.y, t) && t > kNearSphere)
+            MBK_CHECK(ol >= 0 && ol < m && j >= 0 && j < n && r >= 0 && r < kSensor);
+            if (ray_sphere(ray, qi.x - qj.x, qi.y - qj.y, t) && t > kNearSphere) {
+                MBK_CHECK(!FAST || (t >= 1.0f && t < 256.0f));
                 atomicMin(&best[ol * kSensor + r], S::make(t, j));
+            }
         };
         auto run_tests = [&](int first, int count) {
             if (lane < count) {
@@ -960,6 +983,7 @@ __device__ __forceinline__ void export_world(const SimDev &d, int cur, int with_
                 }
                 const uint32_t oi = __shfl_sync(FULL, info, own);
                 const int r = (int)(oi & 31u) + q - __shfl_sync(FULL, exc, own) + 1;   /* candidate 0 was tested above */
+                MBK_CHECK(q >= total || (qn + lane < kQueue && r >= 0 && r < kSensor));
                 if (q < total) queue[qn + lane] = ((oi >> 17) << 5) | (uint32_t)r;
                 qn += max(0, min(32, total - q0));
                 __syncwarp();
@@ -983,6 +1007,7 @@ __device__ __forceinline__ void export_world(const SimDev &d, int cur, int with_
             const uint32_t info = (uint32_t)(rr.lo & 31) | ((uint32_t)rr.count << 5) | (code << 17);
             const bool has = valid && rr.count > 0;
             const unsigned bal = __ballot_sync(FULL, has);
+            MBK_CHECK(pqn + __popc(bal & lt) < kQueue && (!valid || (rr.lo >= 0 && rr.lo + rr.count <= kSensor)));
             if (has) pairq[pqn + __popc(bal & lt)] = info;
             pqn += __popc(bal);
             __syncwarp();
@@ -1008,6 +1033,7 @@ __device__ __forceinline__ void export_world(const SimDev &d, int cur, int with_
                 /* stage 1: is the target anywhere near the two fans? (pair_maybe, sim_prims.cuh) */
                 const bool maybe = pair_maybe(pi.x - pj.x, pi.y - pj.y, Dir{hd.x, hd.y}) && j < jend;
                 const unsigned bal = __ballot_sync(FULL, maybe);
+                MBK_CHECK(cqn + __popc(bal & lt) < kQueue);
                 if (maybe) candq[cqn + __popc(bal & lt)] = ((uint32_t)ol << JB) | (uint32_t)j;
                 cqn += __popc(bal);
                 if (cqn >= 32) {
