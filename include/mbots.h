@@ -141,6 +141,20 @@ int mbots_sync(mbots_sim *sim, void *stream);
 int mbots_rollout_step_async(mbots_sim *sim, const int32_t *actions_dev, uint64_t action_rows, int32_t shift, void *stream);
 /* The action write alone (asynchronous, row count resolved on the device as above). */
 int mbots_write_actions(mbots_sim *sim, const int32_t *actions_dev, uint64_t action_rows, void *stream);
+/* Pointer lifetime -- a deliberate deviation from the reference, whose export base pointers never move
+ * (M/src/mw/cuda_exec.cpp:3075; SURVEY.md 8(b) "fixed addresses"). Here every row-indexed export lives in one of TWO
+ * row sets: a step gathers each agent's record from its old row in one set and writes its new row in the other (that
+ * gather IS the species-major sort, and it cannot be done in place: births and deaths anywhere shift every later row).
+ * Keeping the two caller-writable exports (action, hidden state) at one address would cost a copy-back of 88 B read +
+ * 88 B written per agent and step (+0.07 ms at 2.2 M agents, ~10 % of the step); the choice made is to keep the
+ * ping-pong and make its one hazard detectable: a view fetched before a step points at the DEAD set after it, and a
+ * write through it is lost. The reference's own callers are unaffected -- they re-fetch every tensor after every step
+ * because the leading dimension changes (learn/training_loop.py:47-50,136-137). Debug mode (this call, or
+ * MBOTS_POISON_DEAD_SET=1 in the environment): after every step the dead set's action and hidden-state columns are
+ * filled with a poison pattern, and the next step call first verifies the pattern: a write through a stale view makes
+ * it fail with MBOTS_ESTATE and a message. Costs two small kernels and a host wait per step; off by default. */
+int mbots_debug_stale_views(mbots_sim *sim, int32_t enable);
+
 /* Number of step graphs launched by this handle since creation (bench bookkeeping). */
 int mbots_graph_launch_count(mbots_sim *sim, uint64_t *out);
 

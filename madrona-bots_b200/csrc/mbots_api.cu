@@ -77,6 +77,8 @@ struct mbots_sim {
     struct StepGraph { cudaGraphExec_t exec; int kernels; };
     std::map<ChainKey, StepGraph> graphs;
     uint64_t graphLaunches;
+    /* stale-view detector (MBOTS_POISON_DEAD_SET=1 or mbots_debug_stale_views) */
+    bool poison, poisoned;
 };
 
 namespace {
@@ -278,9 +280,31 @@ int record_chain(mbots_sim *s, const ChainKey &k, cudaStream_t st, bool timing, 
 
 
 
+/* Debug mode: did the caller write the action / hidden-state export through a view it fetched BEFORE the last step?
+ * Those views point at the dead row set, whose two writable columns were poisoned after that step. */
+int check_stale_views(mbots_sim *s, cudaStream_t st)
+{
+    if (!s->poison || !s->poisoned) return MBOTS_OK;
+    unsigned int *bad = s->d.scanSync + 2;
+    launch_poison(s->d, s->cur ^ 1, (size_t)s->d.numWorlds * s->d.cap, 1, bad, st);
+    unsigned int h = 0;
+    CU(cudaMemcpyAsync(&h, bad, sizeof h, cudaMemcpyDeviceToHost, st));
+    CU(cudaStreamSynchronize(st));
+    s->poisoned = false;
+    if (h != 0) {
+        char msg[200];
+        snprintf(msg, sizeof msg, "%u words of the action / hidden-state export were written through a view fetched before "
+                 "the previous step (row exports are re-fetched after every step: include/mbots.h)", h);
+        return fail(MBOTS_ESTATE, msg);
+    }
+    return MBOTS_OK;
+}
+
 int enqueue_step(mbots_sim *s, cudaStream_t st, const void *actions = nullptr, unsigned long long action_rows = 0,
                  int with_shift = 0)
 {
+    int rc0 = check_stale_views(s, st);
+    if (rc0 != MBOTS_OK) return rc0;
     const ChainKey k = chain_key(s, actions, action_rows, with_shift);
     int n = 0;
     if (s->profile || !s->useGraphs) {
@@ -315,6 +339,10 @@ int enqueue_step(mbots_sim *s, cudaStream_t st, const void *actions = nullptr, u
     s->cur ^= 1;
     s->launches += (uint64_t)n;
     s->dirty = true;
+    if (s->poison) {
+        launch_poison(s->d, s->cur ^ 1, (size_t)s->d.numWorlds * s->d.cap, 0, nullptr, st);
+        s->poisoned = true;
+    }
     return MBOTS_OK;
 }
 
@@ -365,6 +393,8 @@ int mbots_create_ex(const mbots_config *cfg, mbots_sim **out)
         if (cudaStreamCreateWithFlags(&s->capStream, cudaStreamNonBlocking) != cudaSuccess) rc = fail(MBOTS_ECUDA, "cudaStreamCreate");
         const char *g = getenv("MBOTS_GRAPHS");
         s->useGraphs = !(g && g[0] == '0');
+        const char *pz = getenv("MBOTS_POISON_DEAD_SET");
+        s->poison = pz && pz[0] == '1';
     }
     if (rc == MBOTS_OK) {
         prepare_kernels(s->d);                  /* shared-memory opt-in for the largest geometry, once, outside any capture */
@@ -424,6 +454,14 @@ int mbots_write_actions(mbots_sim *s, const int32_t *actions_dev, uint64_t actio
     launch_action_write(s->d, s->cur, actions_dev, action_rows, rows, (cudaStream_t)stream);
     CU(cudaGetLastError());
     s->launches += 1;
+    return MBOTS_OK;
+}
+
+int mbots_debug_stale_views(mbots_sim *s, int32_t enable)
+{
+    if (!s) return fail(MBOTS_EINVAL, "null handle");
+    s->poison = enable != 0;
+    s->poisoned = false;
     return MBOTS_OK;
 }
 

@@ -90,6 +90,7 @@ void launch_shift(const SimDev &d, int cur, uint32_t rows_upper, cudaStream_t s)
 void launch_action_write(const SimDev &d, int cur, const void *src, unsigned long long src_rows, uint32_t rows_upper, cudaStream_t s);
 void launch_stats_reduce(const SimDev &d, long long *out16, cudaStream_t s);
 void launch_debug_gather(const SimDev &d, int what, void *out, cudaStream_t s);
+void launch_poison(const SimDev &d, int set, size_t rows, int check, unsigned int *bad, cudaStream_t s);
 void launch_validate_state(const SimDev &d, uint32_t total_agents, unsigned int *flags2, cudaStream_t s);
 /* launchers (policy_kernels.cu) */
 void launch_pack_obs(const ObsSet &o, int is_prev, uint32_t row_begin, uint32_t rows, float *out, cudaStream_t s);

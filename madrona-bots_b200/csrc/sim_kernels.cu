@@ -1417,6 +1417,29 @@ void launch_validate_state(const SimDev &d, uint32_t total_agents, unsigned int 
     validate_state_kernel<<<d.numWorlds, 64, 0, s>>>(d, total_agents, flags2);
 }
 
+/* Debug aid for the pointer-lifetime rule of include/mbots.h (row exports ping-pong between two sets, so a view fetched
+ * before a step points at the DEAD set afterwards): poison the two caller-writable columns of the dead set after a step,
+ * and before the next one count the words that no longer hold the poison -- a write through a stale view. */
+constexpr uint32_t kPoison = 0xDEADA110u;
+__global__ void __launch_bounds__(256) poison_kernel(SimDev d, int set, size_t rows, int check, unsigned int *bad)
+{
+    uint32_t *act = reinterpret_cast<uint32_t *>(d.obs[set].action);
+    uint32_t *hid = reinterpret_cast<uint32_t *>(d.obs[set].hidden);
+    const size_t na = rows * 6, nh = rows * 16, stride = (size_t)gridDim.x * blockDim.x;
+    unsigned int mine = 0;
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < na + nh; i += stride) {
+        uint32_t *p = i < na ? act + i : hid + (i - na);
+        if (check) mine += *p != kPoison; else *p = kPoison;
+    }
+    if (check && mine) atomicAdd(bad, mine);
+}
+
+void launch_poison(const SimDev &d, int set, size_t rows, int check, unsigned int *bad, cudaStream_t s)
+{
+    if (check) cudaMemsetAsync(bad, 0, sizeof(unsigned int), s);
+    poison_kernel<<<148 * 4, 256, 0, s>>>(d, set, rows, check, bad);
+}
+
 void launch_debug_gather(const SimDev &d, int what, void *out, cudaStream_t s)
 {
     debug_gather_kernel<<<d.numWorlds, 128, 0, s>>>(d, what, out);

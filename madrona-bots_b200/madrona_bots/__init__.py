@@ -131,6 +131,11 @@ class SimManager:
         _native.check(self._lib.mbots_write_actions(self._h, ctypes.c_void_p(actions.data_ptr()), int(actions.shape[0]),
                                                     self._stream()), "mbots_write_actions")
 
+    def debug_stale_views(self, enable=True):
+        """Debug mode for the pointer-lifetime rule (include/mbots.h): the next step raises if the action or hidden-state
+        export was written through a view fetched before the previous step."""
+        _native.check(self._lib.mbots_debug_stale_views(self._h, 1 if enable else 0), "mbots_debug_stale_views")
+
     def graph_launch_count(self):
         out = ctypes.c_uint64()
         _native.check(self._lib.mbots_graph_launch_count(self._h, ctypes.byref(out)), "mbots_graph_launch_count")

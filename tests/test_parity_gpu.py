@@ -410,3 +410,29 @@ def test_cuda_path_reproduces_reference_text_rollouts(cuda_device, name):
     np.testing.assert_array_equal(counts, gold[name + ".counts"])
     bad = np.argwhere(digs != gold[name + ".digests"])
     assert len(bad) == 0, f"first mismatch: step {bad[0][0]}, export {REF_EXPORTS[bad[0][1]]}"
+
+
+def test_write_through_a_stale_view_is_detected(cuda_device):
+    """include/mbots.h "Pointer lifetime": row exports ping-pong between two row sets, so a view fetched before a step
+    points at the dead set afterwards. Debug mode poisons the dead set's writable columns and catches the write."""
+    import torch
+    from madrona_bots import SimManager
+    sim = SimManager(0, 16, 3, 32)
+    sim.debug_stale_views(True)
+    sim.step()
+    for _ in range(3):                                   # the reference's pattern: re-fetch after every step -- never trips
+        a = sim.action_tensor(False).to_torch()
+        a.zero_(); a[:, 0] = 1
+        sim.hidden_state_tensor(False).to_torch().fill_(0.5)
+        sim.step()
+    stale = sim.action_tensor(False).to_torch()          # fetched now ...
+    sim.step()                                           # ... dead after this step
+    assert stale.data_ptr() != sim.action_tensor(False).to_torch().data_ptr()
+    stale[:4, 1] = 1                                     # lost write
+    with pytest.raises(RuntimeError, match="stale|before the previous step"):
+        sim.step()
+    sim.step()                                           # the handle stays usable
+    sim.debug_stale_views(False)
+    o, g = make_pair(16, 3, 32)                          # and the mode does not change results
+    g.debug_stale_views(True)
+    drive(o, g, steps=12, seed=1, mode="bits")
