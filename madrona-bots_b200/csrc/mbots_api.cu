@@ -74,6 +74,8 @@ struct mbots_sim {
     /* step graphs */
     bool useGraphs;
     cudaStream_t capStream;        /* capture happens here: the caller's stream may be the legacy default stream */
+    cudaStream_t sideStream[2];    /* forked branches of the captured chain */
+    cudaEvent_t evFork, evJoin[2];
     struct StepGraph { cudaGraphExec_t exec; int kernels; };
     std::map<ChainKey, StepGraph> graphs;
     uint64_t graphLaunches;
@@ -165,6 +167,9 @@ void free_all(mbots_sim *s)
     for (auto &kv : s->graphs) cudaGraphExecDestroy(kv.second.exec);
     s->graphs.clear();
     if (s->capStream) cudaStreamDestroy(s->capStream);
+    for (auto &q : s->sideStream) if (q) cudaStreamDestroy(q);
+    if (s->evFork) cudaEventDestroy(s->evFork);
+    for (auto &e : s->evJoin) if (e) cudaEventDestroy(e);
 }
 
 /* Kernel timing events are read lazily so that profiling never turns an asynchronous call into a blocking one:
@@ -268,12 +273,28 @@ int record_chain(mbots_sim *s, const ChainKey &k, cudaStream_t st, bool timing, 
     if (timing) cudaEventRecord(s->ev[1], st);
     n += 1 + launch_scan(s->d, k.cur, 1, st);
     if (timing) cudaEventRecord(s->ev[2], st);
-    n += launch_export(s->d, k.cur, 1, k.bound, k.actions, k.actionRows, k.withShift, st);
-    if (timing) cudaEventRecord(s->ev[3], st);
-    CU(cudaGetLastError());
-    CU(cudaMemcpyAsync(s->hTotals, s->d.totals, sizeof(Totals), cudaMemcpyDeviceToHost, st));
-    if (external_event) CU(cudaEventRecordWithFlags(s->evTotals, st, cudaEventRecordExternal));
-    else CU(cudaEventRecord(s->evTotals, st));
+    if (external_event) {
+        /* under capture: the totals are final once the scan has run, and the clean-up export touches other worlds than the
+         * fast one -- both fork off onto side streams and join before the step's completion event:
+         *     step -> scan -> { export (fast) | export (full capacity) | 40-byte copy of the totals } -> event */
+        CU(cudaEventRecord(s->evFork, st));
+        CU(cudaStreamWaitEvent(s->sideStream[0], s->evFork, 0));
+        CU(cudaStreamWaitEvent(s->sideStream[1], s->evFork, 0));
+        CU(cudaMemcpyAsync(s->hTotals, s->d.totals, sizeof(Totals), cudaMemcpyDeviceToHost, s->sideStream[1]));
+        n += launch_export(s->d, k.cur, 1, k.bound, k.actions, k.actionRows, k.withShift, st, s->sideStream[0]);
+        CU(cudaGetLastError());
+        CU(cudaEventRecord(s->evJoin[0], s->sideStream[0]));
+        CU(cudaEventRecord(s->evJoin[1], s->sideStream[1]));
+        CU(cudaStreamWaitEvent(st, s->evJoin[0], 0));
+        CU(cudaStreamWaitEvent(st, s->evJoin[1], 0));
+        CU(cudaEventRecordWithFlags(s->evTotals, st, cudaEventRecordExternal));
+    } else {
+        n += launch_export(s->d, k.cur, 1, k.bound, k.actions, k.actionRows, k.withShift, st);
+        if (timing) cudaEventRecord(s->ev[3], st);
+        CU(cudaGetLastError());
+        CU(cudaMemcpyAsync(s->hTotals, s->d.totals, sizeof(Totals), cudaMemcpyDeviceToHost, st));
+        CU(cudaEventRecord(s->evTotals, st));
+    }
     *launches = n;
     return MBOTS_OK;
 }
@@ -391,6 +412,11 @@ int mbots_create_ex(const mbots_config *cfg, mbots_sim **out)
         for (auto &ev : s->evShift) if (cudaEventCreate(&ev) != cudaSuccess) rc = fail(MBOTS_ECUDA, "cudaEventCreate");
         if (cudaEventCreateWithFlags(&s->evTotals, cudaEventDisableTiming) != cudaSuccess) rc = fail(MBOTS_ECUDA, "cudaEventCreate");
         if (cudaStreamCreateWithFlags(&s->capStream, cudaStreamNonBlocking) != cudaSuccess) rc = fail(MBOTS_ECUDA, "cudaStreamCreate");
+        for (auto &q : s->sideStream)
+            if (cudaStreamCreateWithFlags(&q, cudaStreamNonBlocking) != cudaSuccess) rc = fail(MBOTS_ECUDA, "cudaStreamCreate");
+        if (cudaEventCreateWithFlags(&s->evFork, cudaEventDisableTiming) != cudaSuccess) rc = fail(MBOTS_ECUDA, "cudaEventCreate");
+        for (auto &e : s->evJoin)
+            if (cudaEventCreateWithFlags(&e, cudaEventDisableTiming) != cudaSuccess) rc = fail(MBOTS_ECUDA, "cudaEventCreate");
         const char *g = getenv("MBOTS_GRAPHS");
         s->useGraphs = !(g && g[0] == '0');
         const char *pz = getenv("MBOTS_POISON_DEAD_SET");

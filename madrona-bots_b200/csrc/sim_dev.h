@@ -85,7 +85,7 @@ void launch_init(const SimDev &d, cudaStream_t s);
 void launch_step(const SimDev &d, int cur, uint32_t slots, const void *act_src, unsigned long long act_rows, cudaStream_t s);
 int launch_scan(const SimDev &d, int cur, int count_step, cudaStream_t s);
 int launch_export(const SimDev &d, int cur, int with_sensors, uint32_t bound, const void *act_src, unsigned long long act_rows,
-                  int fuse_shift, cudaStream_t s);
+                  int fuse_shift, cudaStream_t s, cudaStream_t s_full = nullptr);
 void launch_shift(const SimDev &d, int cur, uint32_t rows_upper, cudaStream_t s);
 void launch_action_write(const SimDev &d, int cur, const void *src, unsigned long long src_rows, uint32_t rows_upper, cudaStream_t s);
 void launch_stats_reduce(const SimDev &d, long long *out16, cudaStream_t s);

@@ -1359,11 +1359,17 @@ static int export_split_log2(uint32_t numWorlds)
 /* bound: the largest world the caller expects after this step (0 = unknown). Worlds above it are still
  * handled -- by the full kernel -- so a wrong bound costs time, never correctness. Returns the launches made. */
 int launch_export(const SimDev &d, int cur, int with_sensors, uint32_t bound, const void *act_src, unsigned long long act_rows,
-                  int fuse_shift, cudaStream_t s)
+                  int fuse_shift, cudaStream_t s, cudaStream_t s_full)
 {
+    /* s_full: the stream of the full-capacity clean-up launch. The two variants touch disjoint worlds, so under a graph
+     * capture the caller forks it onto a side stream and the (normally empty) clean-up pass leaves the critical path. */
     const StepOpts opts = make_opts(act_src, act_rows, fuse_shift);
     uint32_t fast_slots = (bound + 7u) & ~7u;
-    if (bound == 0 || fast_slots > (uint32_t)kFastSlots || fast_slots > d.cap) {
+    /* a bound beyond what the fast variant can take (64 slots, worlds of up to 63 agents) only means that the largest worlds
+     * go to the full variant -- never that all of them do */
+    if (fast_slots > (uint32_t)kFastSlots) fast_slots = (uint32_t)kFastSlots;
+    if (fast_slots > d.cap) fast_slots = d.cap & ~7u;
+    if (bound == 0 || fast_slots < 8u) {
         launch_export_variant<false>(d, cur, with_sensors, d.cap, kFullTile, -1, 0, opts, s);
         return 1;
     }
@@ -1372,7 +1378,8 @@ int launch_export(const SimDev &d, int cur, int with_sensors, uint32_t bound, co
     uint32_t tile = (uint32_t)MBK_EXPORT_FAST_TILE;
     if (tile > fast_slots) tile = fast_slots;
     launch_export_variant<true>(d, cur, with_sensors, fast_slots, tile, 0, export_split_log2(d.numWorlds), opts, s);
-    launch_export_variant<false>(d, cur, with_sensors, d.cap, kFullTile, (int)(fast_slots < 63u ? fast_slots : 63u), 0, opts, s);
+    launch_export_variant<false>(d, cur, with_sensors, d.cap, kFullTile, (int)(fast_slots < 63u ? fast_slots : 63u), 0, opts,
+                                 s_full ? s_full : s);
     return 2;
 }
 
