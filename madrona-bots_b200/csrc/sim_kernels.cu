@@ -737,7 +737,7 @@ __host__ __device__ inline ExportLayout export_layout(uint32_t slots, uint32_t t
     L.head = o; o += slots * 8;                         /* float2 unit heading (cull only) */
     L.queue = o; o += kQueue * 4;
     L.pairq = o; o += kQueue * 4;
-    L.candq = o; o += kQueue * 4;
+    L.candq = o; o += kQueue * 4;                       /* 128 16-bit (observer, target) codes */
     L.newrow = o; o += slots * 4;
     /* old rows are dead once the columns are carried, the queues idle until then: share the bytes when they fit
      * (FAST: 28 single-warp CTAs of 56 slots then fit one SM's shared memory, not 26) */
@@ -798,10 +798,12 @@ __device__ __forceinline__ void carry_column(void *dst, const void *src, const i
  * share [n * split / nsplit, n * (split + 1) / nsplit) of the agents. No synchronisation between the parts; a step of a
  * small launch is then not bounded by one warp walking a whole world's sensor pass.
  * `my` = this warp's shared memory (export_layout). */
-template <bool FAST>
+template <bool FAST, bool SPLIT, bool FUSED>
 __device__ __forceinline__ void export_world(const SimDev &d, int cur, int with_sensors, uint32_t slots, uint32_t tile,
                                              uint32_t w, int n, unsigned char *my, int split, int nsplit, const StepOpts &opts)
 {
+    /* SPLIT and FUSED are compile-time: the common launch (whole world per warp) carries none of the part bookkeeping,
+     * and the fused-shift variant none of the old prev-row loads (64 registers are tight) */
     typedef Sense<FAST> S;
     typedef typename S::Key Key;
     const int lane = threadIdx.x & 31;
@@ -811,7 +813,7 @@ __device__ __forceinline__ void export_world(const SimDev &d, int cur, int with_
     float2 *head = reinterpret_cast<float2 *>(my + L.head);
     uint32_t *queue = reinterpret_cast<uint32_t *>(my + L.queue);
     uint32_t *pairq = reinterpret_cast<uint32_t *>(my + L.pairq);
-    uint32_t *candq = reinterpret_cast<uint32_t *>(my + L.candq);
+    uint16_t *candq = reinterpret_cast<uint16_t *>(my + L.candq);
     int *newrow = reinterpret_cast<int *>(my + L.newrow);
     int *oldrow = reinterpret_cast<int *>(my + L.oldrow);
     float *theta = reinterpret_cast<float *>(my + L.theta);
@@ -824,7 +826,7 @@ __device__ __forceinline__ void export_world(const SimDev &d, int cur, int with_
     const int off = d.worldOffset[w];
     const float4 srew = d.speciesReward[w];
     const unsigned lt = (1u << lane) - 1u;
-    const int a_lo = (n * split) / nsplit, a_hi = (n * (split + 1)) / nsplit;   /* this part's agents */
+    const int a_lo = SPLIT ? (n * split) / nsplit : 0, a_hi = SPLIT ? (n * (split + 1)) / nsplit : n;   /* this part's agents */
 
     if (FAST && lane == 0) spec[63] = 0xffu;            /* species byte a missed ray decodes to (n <= 63) */
     /* ---- per agent (one lane each): new row, observation exports, small carried columns ---- */
@@ -851,14 +853,14 @@ __device__ __forceinline__ void export_world(const SimDev &d, int cur, int with_
         if (on) {
             const int row = comp(rb, sp - 1) + rank;
             const int old = __float_as_int(sc.x);
-            const bool mine = s >= a_lo && s < a_hi;
+            const bool mine = !SPLIT || (s >= a_lo && s < a_hi);
             MBK_CHECK((uint32_t)s < slots && sp >= 1 && sp <= 4 && row >= 0 && (uint32_t)row < d.numWorlds * d.cap);
             MBK_CHECK(old >= -1 && (old < 0 || (uint32_t)old < d.numWorlds * d.cap));
             /* carried small columns: issue the loads first */
             int4 pst = make_int4(0, 0, 0, 0);
             float2 ppos = make_float2(0.f, 0.f), psur = make_float2(0.f, 0.f);
             float prew = 0.f, phl = 0.f;
-            if (old >= 0 && mine && !opts.fuseShift) {
+            if (old >= 0 && mine && !FUSED) {
                 pst = reinterpret_cast<const int4 *>(from.prev_stats)[old];
                 ppos = reinterpret_cast<const float2 *>(from.prev_position)[old];
                 psur = reinterpret_cast<const float2 *>(from.prev_surrounding)[old];
@@ -882,7 +884,7 @@ __device__ __forceinline__ void export_world(const SimDev &d, int cur, int with_
                 const float sterm = sp == 1 ? srew.x : sp == 2 ? srew.y : sp == 3 ? srew.z : srew.w;
                 const float rew = with_sensors ? agent_reward(sterm, hp, (st & 4u) != 0, (st & 8u) != 0, (st & 2u) != 0) : 0.f;
                 to.reward[row] = rew;
-                if (opts.fuseShift) {                   /* shiftObservationsSystem (:1018-1036) incl. the U7 field mix-up */
+                if (FUSED) {                            /* shiftObservationsSystem (:1018-1036) incl. the U7 field mix-up */
                     pst = make_int4(st & 1u, st & 1u, (st >> 2) & 1u, (st >> 3) & 1u);
                     ppos = make_float2(p.x, p.y);
                     psur = make_float2(sc.y, sc.z);
@@ -905,7 +907,7 @@ __device__ __forceinline__ void export_world(const SimDev &d, int cur, int with_
     /* ---- the sort: the wide columns of the observation record follow their agent ---- */
     const int na = a_hi - a_lo;
     const int *nr = newrow + a_lo, *orow = oldrow + a_lo;
-    if (opts.fuseShift) {                               /* shiftHiddenState (:1039-1048), prev_action (:1025-1030): one read, two writes */
+    if (FUSED) {                                        /* shiftHiddenState (:1039-1048), prev_action (:1025-1030): one read, two writes */
         carry_column<float4, 4, 3>(to.hidden, from.hidden, nr, orow, na, lane, to.prev_hidden);
         carry_column<int2, 3, 4>(to.action, from.action, nr, orow, na, lane, to.prev_action, opts.actSrc, opts.actRows);
     } else {
@@ -1027,24 +1029,29 @@ __device__ __forceinline__ void export_world(const SimDev &d, int cur, int with_
             const int ol = sub0 + (on_i ? il : 0);      /* observer within the tile */
             const float2 pi = pos[tile0 + ol], hd = head[tile0 + ol];
             const int jend = on_i ? n : 0;
-            for (int j0 = 0; j0 < n; j0 += tpi) {
-                const int j = j0 + jl;
-                const float2 pj = pos[min(j, n - 1)];
+            /* two targets per trip: both position loads and both wedge tests are in flight together, and the queue
+             * bookkeeping (counter, branch) is paid once; the queue of 16-bit codes holds < 32 + 64 entries */
+            for (int j0 = 0; j0 < n; j0 += 2 * tpi) {
+                const int ja = j0 + jl, jb = ja + tpi;
+                const float2 pa = pos[min(ja, n - 1)], pb = pos[min(jb, n - 1)];
                 /* stage 1: is the target anywhere near the two fans? (pair_maybe, sim_prims.cuh) */
-                const bool maybe = pair_maybe(pi.x - pj.x, pi.y - pj.y, Dir{hd.x, hd.y}) && j < jend;
-                const unsigned bal = __ballot_sync(FULL, maybe);
-                MBK_CHECK(cqn + __popc(bal & lt) < kQueue);
-                if (maybe) candq[cqn + __popc(bal & lt)] = ((uint32_t)ol << JB) | (uint32_t)j;
-                cqn += __popc(bal);
-                if (cqn >= 32) {
+                const bool ma = pair_maybe(pi.x - pa.x, pi.y - pa.y, Dir{hd.x, hd.y}) && ja < jend;
+                const bool mb = pair_maybe(pi.x - pb.x, pi.y - pb.y, Dir{hd.x, hd.y}) && jb < jend;
+                const unsigned ba = __ballot_sync(FULL, ma), bb = __ballot_sync(FULL, mb);
+                const int ca = __popc(ba);
+                MBK_CHECK(cqn + ca + __popc(bb) <= 2 * kQueue);
+                if (ma) candq[cqn + __popc(ba & lt)] = (uint16_t)(((uint32_t)ol << JB) | (uint32_t)ja);
+                if (mb) candq[cqn + ca + __popc(bb & lt)] = (uint16_t)(((uint32_t)ol << JB) | (uint32_t)jb);
+                cqn += ca + __popc(bb);
+                while (cqn >= 32) {
                     __syncwarp();
                     cqn -= 32;
-                    spans(candq[cqn + lane], true);
+                    spans((uint32_t)candq[cqn + lane], true);
                 }
             }
         }
         __syncwarp();
-        spans(lane < cqn ? candq[lane] : 0u, lane < cqn);
+        spans(lane < cqn ? (uint32_t)candq[lane] : 0u, lane < cqn);
         expand(lane < pqn ? pairq[lane] : 0u, lane < pqn, true);
         __syncwarp();                                   /* the decode below reads keys other lanes wrote with atomicMin */
 
@@ -1096,7 +1103,7 @@ __device__ __forceinline__ void export_world(const SimDev &d, int cur, int with_
 /* skip: FAST -> worlds with more than `slots` agents are left to the full kernel;
  *       full -> worlds with at most `skip_upto` agents were done by the FAST kernel (grid-stride over the
  *               worlds with a small grid, and nothing at all when no world is that large). */
-template <bool FAST>
+template <bool FAST, bool SPLIT, bool FUSED>
 __global__ void __launch_bounds__(kExportWarps * 32, FAST ? kExportFastMinBlocks : 16 / kExportWarps)
 export_kernel(SimDev d, int cur, int with_sensors, uint32_t slots, uint32_t tile, int skip_upto, int split_log2, StepOpts opts)
 {
@@ -1110,12 +1117,13 @@ export_kernel(SimDev d, int cur, int with_sensors, uint32_t slots, uint32_t tile
         if (w >= d.numWorlds) return;               /* whole warp: no block-level barrier anywhere */
         const int n = d.worldCount[w];
         if (n > (int)slots || n > 63) return;       /* slot 63 is the miss sentinel of the 32-bit keys */
-        export_world<FAST>(d, cur, with_sensors, slots, tile, w, n, my, (int)(unit & ((1u << split_log2) - 1u)), 1 << split_log2, opts);
+        export_world<FAST, SPLIT, FUSED>(d, cur, with_sensors, slots, tile, w, n, my, (int)(unit & ((1u << split_log2) - 1u)),
+                                         1 << split_log2, opts);
     } else {
         for (uint32_t w = blockIdx.x * kExportWarps + warp; w < d.numWorlds; w += gridDim.x * kExportWarps) {
             const int n = d.worldCount[w];
             if (n <= skip_upto) continue;
-            export_world<FAST>(d, cur, with_sensors, slots, tile, w, n, my, 0, 1, opts);
+            export_world<FAST, false, FUSED>(d, cur, with_sensors, slots, tile, w, n, my, 0, 1, opts);
             __syncwarp();
         }
     }
@@ -1292,7 +1300,8 @@ void prepare_kernels(const SimDev &d)
         granted[dev][0] = s1;
     }
     if (s2 > 48 * 1024 && s2 > granted[dev][1]) {
-        cudaFuncSetAttribute(export_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)s2);
+        cudaFuncSetAttribute(export_kernel<false, false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)s2);
+        cudaFuncSetAttribute(export_kernel<false, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)s2);
         granted[dev][1] = s2;
     }
 }
@@ -1330,6 +1339,13 @@ int launch_scan(const SimDev &d, int cur, int count_step, cudaStream_t s)
     return 2;
 }
 
+template <bool FAST, bool SPLIT, bool FUSED>
+static void launch_export_inst(const SimDev &d, int cur, int with_sensors, uint32_t slots, uint32_t tile, int skip_upto,
+                               int split_log2, const StepOpts &opts, uint32_t grid, size_t smem, cudaStream_t s)
+{
+    export_kernel<FAST, SPLIT, FUSED><<<grid, kExportWarps * 32, smem, s>>>(d, cur, with_sensors, slots, tile, skip_upto, split_log2, opts);
+}
+
 template <bool FAST>
 static void launch_export_variant(const SimDev &d, int cur, int with_sensors, uint32_t slots, uint32_t tile, int skip_upto,
                                   int split_log2, const StepOpts &opts, cudaStream_t s)
@@ -1337,7 +1353,14 @@ static void launch_export_variant(const SimDev &d, int cur, int with_sensors, ui
     const size_t smem = export_smem_bytes(slots, tile, FAST);
     uint32_t grid = ((d.numWorlds << split_log2) + kExportWarps - 1) / kExportWarps;
     if (!FAST && skip_upto >= 0 && grid > 148u * 4u) grid = 148u * 4u;   /* clean-up pass: few worlds, if any */
-    export_kernel<FAST><<<grid, kExportWarps * 32, smem, s>>>(d, cur, with_sensors, slots, tile, skip_upto, split_log2, opts);
+    const bool split = FAST && split_log2 > 0, fused = opts.fuseShift != 0;
+    if (split) {
+        if (fused) launch_export_inst<FAST, FAST, true>(d, cur, with_sensors, slots, tile, skip_upto, split_log2, opts, grid, smem, s);
+        else launch_export_inst<FAST, FAST, false>(d, cur, with_sensors, slots, tile, skip_upto, split_log2, opts, grid, smem, s);
+    } else {
+        if (fused) launch_export_inst<FAST, false, true>(d, cur, with_sensors, slots, tile, skip_upto, 0, opts, grid, smem, s);
+        else launch_export_inst<FAST, false, false>(d, cur, with_sensors, slots, tile, skip_upto, 0, opts, grid, smem, s);
+    }
 }
 
 /* Parts per world of the FAST export kernel (log2): a full GPU wants ~32 resident single-warp CTAs per SM; below that a
