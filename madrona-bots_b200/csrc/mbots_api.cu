@@ -384,7 +384,7 @@ int mbots_create_ex(const mbots_config *cfg, mbots_sim **out)
     cap = (cap + 31u) & ~31u;
     if (cap < cfg->init_num_agents_per_world || cap > 1024u)
         return fail(MBOTS_EINVAL, "per-world capacity must hold the initial agents and be <= 1024");
-    if ((uint64_t)cfg->num_worlds * cap > 0x7fffffffull) return fail(MBOTS_EINVAL, "num_worlds * capacity exceeds int32 rows");
+    if ((uint64_t)cfg->num_worlds * cap > 0x1fffffffull) return fail(MBOTS_EINVAL, "num_worlds * capacity exceeds 2^29 rows");
     int ndev = 0;
     cudaError_t e = cudaGetDeviceCount(&ndev);
     if (e != cudaSuccess || ndev == 0) return fail(MBOTS_ECUDA, "no CUDA device (this library has no CPU path)", e);

@@ -771,7 +771,7 @@ __device__ __forceinline__ void carry_column(void *dst, const void *src, const i
     const V *ep = reinterpret_cast<const V *>(ext);
     for (int t0 = lane; t0 < tasks; t0 += 32 * UNROLL) {
         V v[UNROLL];
-        size_t di[UNROLL];
+        uint32_t di[UNROLL];                            /* rows * PARTS < 2^32: mbots_create bounds the row capacity */
 #pragma unroll
         for (int u = 0; u < UNROLL; ++u) {
             const int t = t0 + 32 * u;
@@ -780,7 +780,7 @@ __device__ __forceinline__ void carry_column(void *dst, const void *src, const i
             if (t < tasks) {
                 const int a = t / PARTS, p = t - a * PARTS;
                 const int o = oldrow[a];
-                di[u] = (size_t)newrow[a] * PARTS + p;
+                di[u] = (uint32_t)newrow[a] * PARTS + p;
                 if (o >= 0) v[u] = (ep != nullptr && (unsigned long long)o < ext_rows ? ep : sp)[(size_t)o * PARTS + p];
             }
         }
@@ -1324,13 +1324,24 @@ void launch_step(const SimDev &d, int cur, uint32_t slots, const void *act_src, 
 }
 
 /* Returns the kernels launched: one (scan_fused_kernel) while every tile's CTA fits on the GPU at once -- its grid-wide
- * barrier needs that; 148 SMs x one 1,024-thread CTA = 151,552 worlds -- otherwise tile sums and row scan as two. */
+ * barrier needs that (SM count x occupancy, queried per device: >= 151,552 worlds on a B200) -- otherwise tile sums and
+ * row scan as two. */
 int launch_scan(const SimDev &d, int cur, int count_step, cudaStream_t s)
 {
     const unsigned tiles = (d.numWorlds + kScanTile - 1) / kScanTile;
     static int fused = -1;
+    static unsigned resident[64];                       /* per device: CTAs of scan_fused_kernel the GPU holds at once */
     if (fused < 0) { const char *e = getenv("MBOTS_SCAN_FUSED"); fused = !(e && e[0] == '0'); }
-    if (fused && tiles <= 148u && d.scanSync != nullptr) {
+    int dev = 0;
+    cudaGetDevice(&dev);
+    dev &= 63;
+    if (resident[dev] == 0) {
+        int sms = 0, per_sm = 0;
+        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, scan_fused_kernel, kScanTile, 0);
+        resident[dev] = (unsigned)(sms > 0 && per_sm > 0 ? sms * per_sm : 1);
+    }
+    if (fused && tiles <= resident[dev] && d.scanSync != nullptr) {
         scan_fused_kernel<<<tiles, kScanTile, 0, s>>>(d, cur, count_step, d.scanSync);
         return 1;
     }

@@ -280,10 +280,17 @@ struct RaySpan { int flo, fhi, blo, bhi; };
 constexpr float kCullMinDist2 = 1.2f;        /* D < 1.095: t <= D < 1.1, nothing can be accepted */
 constexpr float kCullAngleMargin = 5e-4f;    /* rad; covers the 1e-5 rad of cull_atan2 and the approximate division */
 
+/* single-instruction approximations for the cull (MUFU.RSQ / MUFU.RCP with flush-to-zero: without -use_fast_math
+ * rsqrtf() and __fdividef() carry range-scaling code around them; the cull's operands are never denormal or huge) */
+#if defined(__CUDA_ARCH__)
+__device__ __forceinline__ float cull_rsqrt(float v) { float r; asm("rsqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(v)); return r; }
+__device__ __forceinline__ float cull_rcp(float v) { float r; asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(v)); return r; }
+#endif
+
 MBP_HD float inv_sqrt_upper(float v)
 {
 #if defined(__CUDA_ARCH__)
-    return rsqrtf(v) * 1.0005f;
+    return cull_rsqrt(v) * 1.0005f;
 #else
     return (1.f / sqrtf(v)) * 1.0005f;
 #endif
@@ -295,7 +302,7 @@ MBP_HD Dir cull_heading(Rot r)
 {
     const Dir f = rot_forward(r);
 #if defined(__CUDA_ARCH__)
-    const float inv = rsqrtf(f.x * f.x + f.y * f.y);
+    const float inv = cull_rsqrt(f.x * f.x + f.y * f.y);
 #else
     const float inv = 1.f / sqrtf(f.x * f.x + f.y * f.y);
 #endif
@@ -308,7 +315,7 @@ MBP_HD float cull_atan2(float y, float x)
     const float ax = fabsf(x), ay = fabsf(y);
     const float mx = fmaxf(ax, ay), mn = fminf(ax, ay);
 #if defined(__CUDA_ARCH__)
-    const float q = __fdividef(mn, mx);
+    const float q = mn * cull_rcp(mx);
 #else
     const float q = mn / mx;
 #endif
