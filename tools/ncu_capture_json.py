@@ -33,7 +33,8 @@ def main():
     kernels = {}
     for r in rows[2:]:
         name = r[col["Kernel Name"]]
-        key = ("export_kernel" if "export_kernel<1>" in name or "export_kernel<(bool)1>" in name else
+        fast = any(t in name for t in ("export_kernel<1>", "export_kernel<(bool)1>", "export_kernel<1,", "export_kernel<(bool)1,"))
+        key = ("export_kernel" if fast else
                "step_kernel" if "step_kernel" in name else "shift_kernel" if "shift_kernel" in name else
                "scan_kernel" if "scan_kernel" in name else "tile_sum_kernel" if "tile_sum" in name else
                "action_write_kernel" if "action_write" in name else None)
