@@ -70,7 +70,8 @@ enum mbots_export_id {
     MBOTS_DEBUG_AGENT_HEALTH,          /* int32  (A, 1) agent order */
     MBOTS_DEBUG_AGENT_SPECIES,         /* int32  (A, 1) agent order */
     MBOTS_DEBUG_AGENT_TARGET,          /* int32  (A, 1) finder hit as slot in own world, -1 none */
-    MBOTS_DEBUG_ROW_BASE               /* int32  (numWorlds, 4) first obs row of (world, species) */
+    MBOTS_DEBUG_ROW_BASE,              /* int32  (numWorlds, 4) first obs row of (world, species) */
+    MBOTS_DEBUG_ROW_OWNER              /* int32  (A, 1) observation row -> (local world << 10) | slot of the agent that owns it */
 };
 
 enum mbots_dtype {
@@ -223,10 +224,11 @@ int mbots_load_state(mbots_sim *sim, const void *host, uint64_t bytes, void *str
  *   selects the prev_* exports) to the device buffer `out`.
  * mbots_sample_actions: learn/training_loop.py:57,77-83,136 -- Categorical sample + one-hot write-back.
  *   `weights` is a device (n, 6) float32 matrix of non-negative action weights (softmax of the logits; need
- *   not be normalised). Row r draws u = uniform(split(split(init(seed), draw), row_begin + r)) with the
- *   simulator's Threefry (M/include/madrona/rand.inl) and takes the first k with u * sum(w) < w0 + .. + wk
- *   (sums in index order, fp32, no FMA), then stores the int32 one-hot row into the action export. The picked
- *   index also goes to out_index[r] when that is not NULL. Deterministic in (seed, draw, row). */
+ *   not be normalised). Row r draws u = uniform(split(split(init(seed), draw), id, id >> 32)) with the
+ *   simulator's Threefry (M/include/madrona/rand.inl), id = (GLOBAL world id << 10) | slot of the agent that owns the
+ *   row, and takes the first k with u * sum(w) < w0 + .. + wk (sums in index order, fp32, no FMA), then stores the
+ *   int32 one-hot row into the action export. The picked index also goes to out_index[r] when that is not NULL.
+ *   Deterministic in (seed, draw, agent): an agent's draw does not depend on how the worlds are sharded over handles. */
 int mbots_pack_observations(mbots_sim *sim, int32_t is_prev, uint32_t row_begin, uint32_t row_end, float *out,
                             void *stream);
 int mbots_sample_actions(mbots_sim *sim, uint32_t row_begin, uint32_t row_end, const float *weights, uint32_t seed,
@@ -234,7 +236,7 @@ int mbots_sample_actions(mbots_sim *sim, uint32_t row_begin, uint32_t row_end, c
 
 /* The whole acting path of learn/training_loop.py:52-83,136 for rows [row_begin, row_end) as ONE kernel:
  * construct_obs -> species network (mbots_policy.h program over a device blob of bf16 weights) -> softmax ->
- * Categorical sample (same stream as mbots_sample_actions: keyed seed, draw, row) -> one-hot row in the action
+ * Categorical sample (same stream as mbots_sample_actions: keyed seed, draw, agent) -> one-hot row in the action
  * export. Tensor-core products (bf16 in, fp32 accumulate); activations never leave the SM between layers.
  * program->layout picks the kernel: MBOTS_LAYOUT_SW128 = tcgen05.mma + tensor memory (policy_umma.cu),
  * MBOTS_LAYOUT_ROWPAD = mma.sync (policy_fused.cu); the blob must be laid out accordingly (mbots_policy.h).

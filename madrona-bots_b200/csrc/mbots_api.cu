@@ -124,6 +124,8 @@ int alloc_obs(mbots_sim *s, ObsSet &o, size_t rows)
     ALLOC(o.stats, rows * 4); ALLOC(o.prev_stats, rows * 4);
     ALLOC(o.semantic, rows * 32); ALLOC(o.prev_semantic, rows * 32);
     ALLOC(o.depth, rows * 32); ALLOC(o.prev_depth, rows * 32);
+    ALLOC(o.owner, rows);
+    o.worldIdOffset = s->d.worldIdOffset;
     return MBOTS_OK;
 }
 
@@ -382,6 +384,7 @@ int mbots_create_ex(const mbots_config *cfg, mbots_sim **out)
         if (cap < 128u) cap = 128u;
     }
     cap = (cap + 31u) & ~31u;
+    if (cfg->num_worlds > (1u << 22)) return fail(MBOTS_EINVAL, "num_worlds must be <= 4,194,304 per handle");
     if (cap < cfg->init_num_agents_per_world || cap > 1024u)
         return fail(MBOTS_EINVAL, "per-world capacity must hold the initial agents and be <= 1024");
     if ((uint64_t)cfg->num_worlds * cap > 0x1fffffffull) return fail(MBOTS_EINVAL, "num_worlds * capacity exceeds 2^29 rows");
@@ -596,6 +599,7 @@ int mbots_tensor(mbots_sim *s, int32_t id, void **dev_ptr, int64_t dims[2], int3
     case MBOTS_DEBUG_NUM_FOOD: return set(s->d.numFood, W, 1, MBOTS_I32);
     case MBOTS_DEBUG_FOOD: return set(s->d.food, W * 48, 8, MBOTS_U8);
     case MBOTS_DEBUG_ROW_BASE: return set(s->d.rowBase[s->cur], W, 4, MBOTS_I32);
+    case MBOTS_DEBUG_ROW_OWNER: return set(o.owner, A, 1, MBOTS_I32);
     case MBOTS_DEBUG_POSE: return gather(0, 4, MBOTS_F32);
     case MBOTS_DEBUG_AGENT_HEALTH: return gather(1, 1, MBOTS_I32);
     case MBOTS_DEBUG_AGENT_SPECIES: return gather(2, 1, MBOTS_I32);
@@ -743,6 +747,7 @@ void ckpt_segments(mbots_sim *s, int set, size_t A, std::vector<Segment> &out)
     add(o.health, A * 4); add(o.prev_health, A * 4); add(o.surrounding, A * 8); add(o.prev_surrounding, A * 8);
     add(o.stats, A * 16); add(o.prev_stats, A * 16); add(o.semantic, A * 32); add(o.prev_semantic, A * 32);
     add(o.depth, A * 32); add(o.prev_depth, A * 32);
+    add(o.owner, A * 4);
 }
 
 uint64_t ckpt_total(const std::vector<Segment> &segs)
@@ -838,6 +843,7 @@ int mbots_load_state(mbots_sim *s, const void *host, uint64_t bytes, void *strea
         }
     }
     s->d.worldIdOffset = h.worldIdOffset; s->d.seed = h.seed;
+    s->d.obs[0].worldIdOffset = s->d.obs[1].worldIdOffset = h.worldIdOffset;
     for (auto &kv : s->graphs) cudaGraphExecDestroy(kv.second.exec);      /* the SimDev is baked into every kernel node */
     s->graphs.clear();
     s->cur = 0;

@@ -20,11 +20,20 @@ __device__ __forceinline__ float obs_element(const uint8_t *__restrict__ depth, 
     return surrounding[row * 2 + (c - 67u)];
 }
 
-/* u = uniform(split(draw_key, row)); action = first k with u * total < w0 + ... + wk (sums in index order);
- * stores the one-hot int32 row `row` of the action export and returns the pick. */
-__device__ __forceinline__ int sample_and_write(const float (&w)[6], Key draw_key, uint32_t row, int32_t *__restrict__ action)
+/* The agent that owns observation row `row`, as a shard-invariant 64-bit id: (GLOBAL world id << 10) | slot. */
+__device__ __forceinline__ unsigned long long agent_id(const uint32_t *__restrict__ owner, uint32_t world_off, uint32_t row)
 {
-    const float u = key_sample_uniform(key_split(draw_key, row));
+    const uint32_t o = owner[row];
+    return ((unsigned long long)(world_off + (o >> 10)) << 10) | (unsigned long long)(o & 1023u);
+}
+
+/* u = uniform(split(draw_key, agent id)); action = first k with u * total < w0 + ... + wk (sums in index order);
+ * stores the one-hot int32 row `row` of the action export and returns the pick. Keyed on the agent's (global world,
+ * slot), not on the row number: the same agent draws the same number however the worlds are sharded over GPUs. */
+__device__ __forceinline__ int sample_and_write(const float (&w)[6], Key draw_key, unsigned long long id, uint32_t row,
+                                                int32_t *__restrict__ action)
+{
+    const float u = key_sample_uniform(key_split(draw_key, (uint32_t)id, (uint32_t)(id >> 32)));
     float total = w[0];
 #pragma unroll
     for (int k = 1; k < 6; ++k) total = total + w[k];

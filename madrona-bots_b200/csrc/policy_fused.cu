@@ -131,7 +131,8 @@ struct FusedPlan {                        /* weight blocks in streaming order */
     uint8_t gate_of[3 * MBOTS_POLICY_MAX_OPS];    /* its index within that op (recurrent gates) */
 };
 
-struct ObsPtrs { const uint8_t *depth; const float *health; const float *position; const int8_t *semantic; const float *surrounding; };
+struct ObsPtrs { const uint8_t *depth; const float *health; const float *position; const int8_t *semantic; const float *surrounding;
+                 const uint32_t *owner; uint32_t worldOff; };
 
 __global__ void __launch_bounds__(kFusedThreads, 1)
 policy_fused_kernel(ObsPtrs o, int32_t *__restrict__ action, uint32_t row_begin, uint32_t rows, const unsigned char *__restrict__ blob,
@@ -331,7 +332,8 @@ policy_fused_kernel(ObsPtrs o, int32_t *__restrict__ action, uint32_t row_begin,
                         float wgt[6];
 #pragma unroll
                         for (int k = 0; k < 6; ++k) wgt[k] = __expf(l[k] - m);
-                        const int pick = sample_and_write(wgt, draw_key, row_begin + (uint32_t)lr, action);
+                        const uint32_t srow = row_begin + (uint32_t)lr;
+                        const int pick = sample_and_write(wgt, draw_key, agent_id(o.owner, o.worldOff, srow), srow, action);
                         if (out_index) out_index[lr] = pick;
                     }
                 }
@@ -391,7 +393,7 @@ const char *launch_policy_fused(const ObsSet &o, uint32_t row_begin, uint32_t ro
     const uint32_t tiles = (rows + kTileRows - 1) / kTileRows;
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
     const uint32_t grid = tiles < (uint32_t)sms ? tiles : (uint32_t)sms;      /* persistent: one CTA per SM */
-    const ObsPtrs ptrs = {o.depth, o.health, o.position, o.semantic, o.surrounding};
+    const ObsPtrs ptrs = {o.depth, o.health, o.position, o.semantic, o.surrounding, o.owner, o.worldIdOffset};
     policy_fused_kernel<<<grid, kFusedThreads, smem, s>>>(ptrs, o.action, row_begin, rows,
                                                           static_cast<const unsigned char *>(blob), prog, plan, seed, draw,
                                                           do_sample, out_logits, out_index);

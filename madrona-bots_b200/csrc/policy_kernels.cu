@@ -34,8 +34,9 @@ __global__ void __launch_bounds__(256) pack_obs_kernel(const uint8_t *__restrict
 }
 
 /* weights: (rows, 6) non-negative float32 (probabilities need not be normalised).
- * u = uniform(split(split(init(seed), draw), row)); action = first k with u * total < w0 + ... + wk. */
+ * u = uniform(split(split(init(seed), draw), agent id)); action = first k with u * total < w0 + ... + wk. */
 __global__ void __launch_bounds__(256) sample_kernel(const float *__restrict__ weights, int32_t *__restrict__ action,
+                                                     const uint32_t *__restrict__ owner, uint32_t world_off,
                                                      uint32_t row_begin, uint32_t rows, uint32_t seed, uint32_t draw,
                                                      int32_t *__restrict__ out_index)
 {
@@ -45,7 +46,7 @@ __global__ void __launch_bounds__(256) sample_kernel(const float *__restrict__ w
     const float2 w01 = wp[0], w23 = wp[1], w45 = wp[2];
     const float w[6] = {w01.x, w01.y, w23.x, w23.y, w45.x, w45.y};
     const uint32_t row = row_begin + r;
-    const int pick = sample_and_write(w, key_split(key_init(seed), draw), row, action);
+    const int pick = sample_and_write(w, key_split(key_init(seed), draw), agent_id(owner, world_off, row), row, action);
     if (out_index) out_index[r] = pick;
 }
 
@@ -67,7 +68,7 @@ void launch_sample(const ObsSet &o, uint32_t row_begin, uint32_t rows, const flo
                    int32_t *out_index, cudaStream_t s)
 {
     if (rows == 0) return;
-    sample_kernel<<<(rows + 255) / 256, 256, 0, s>>>(weights, o.action, row_begin, rows, seed, draw, out_index);
+    sample_kernel<<<(rows + 255) / 256, 256, 0, s>>>(weights, o.action, o.owner, o.worldIdOffset, row_begin, rows, seed, draw, out_index);
 }
 
 } // namespace mbk

@@ -277,7 +277,8 @@ struct UmmaPlan {                          /* weight blocks (32 KB each) in stre
     uint16_t bias_n[MBOTS_POLICY_MAX_OPS];
 };
 
-struct UObsPtrs { const uint8_t *depth; const float *health; const float *position; const int8_t *semantic; const float *surrounding; };
+struct UObsPtrs { const uint8_t *depth; const float *health; const float *position; const int8_t *semantic; const float *surrounding;
+                  const uint32_t *owner; uint32_t worldOff; };
 
 __global__ void __launch_bounds__(kUThreads, 1)     /* 17 warps are allocated as 20: 96 registers per thread is the ceiling */
 policy_umma_kernel(UObsPtrs o, int32_t *__restrict__ action, uint32_t row_begin, uint32_t rows, const unsigned char *__restrict__ blob,
@@ -416,7 +417,8 @@ policy_umma_kernel(UObsPtrs o, int32_t *__restrict__ action, uint32_t row_begin,
                             float wgt[6];
 #pragma unroll
                             for (int k = 0; k < 6; ++k) wgt[k] = __expf(l[k] - m);
-                            const int pick = sample_and_write(wgt, draw_key, row_begin + (uint32_t)lr, action);
+                            const uint32_t srow = row_begin + (uint32_t)lr;
+                            const int pick = sample_and_write(wgt, draw_key, agent_id(o.owner, o.worldOff, srow), srow, action);
                             if (out_index) out_index[lr] = pick;
                         }
                     }
@@ -541,7 +543,7 @@ const char *launch_policy_umma(const ObsSet &o, uint32_t row_begin, uint32_t row
     const uint32_t pairs = ((rows + kUTile - 1) / kUTile + 1) / 2;
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
     const uint32_t grid = pairs < (uint32_t)sms ? pairs : (uint32_t)sms;      /* persistent: one CTA per SM */
-    const UObsPtrs ptrs = {o.depth, o.health, o.position, o.semantic, o.surrounding};
+    const UObsPtrs ptrs = {o.depth, o.health, o.position, o.semantic, o.surrounding, o.owner, o.worldIdOffset};
     policy_umma_kernel<<<grid, kUThreads, kUSmemBytes, s>>>(ptrs, o.action, row_begin, rows, static_cast<const unsigned char *>(blob),
                                                             prog, plan, seed, draw, do_sample, out_logits, out_index);
     return nullptr;

@@ -28,6 +28,10 @@ struct ObsSet {
     int32_t *stats, *prev_stats;          /* 4 */
     int8_t *semantic, *prev_semantic;     /* 32 */
     uint8_t *depth, *prev_depth;          /* 32 */
+    /* row -> (local world << 10) | slot of the agent that owns the row (written by the export kernel): the identity
+     * the policy's action sampling is keyed on, so that an agent's draw does not depend on how worlds are sharded */
+    uint32_t *owner;
+    uint32_t worldIdOffset;               /* global id of local world 0 (copy of SimDev::worldIdOffset) */
 };
 
 /* Per-world cumulative event counters (episode statistics). */

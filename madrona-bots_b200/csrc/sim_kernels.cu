@@ -893,6 +893,7 @@ __device__ __forceinline__ void export_world(const SimDev &d, int cur, int with_
                 }
                 d.sensorIndex[off + s] = row;
                 d.row[base + s] = row;
+                to.owner[row] = (w << 10) | (uint32_t)s;
                 if (!with_sensors) d.target[base + s] = (int16_t)-1;
                 reinterpret_cast<int4 *>(to.prev_stats)[row] = pst;
                 reinterpret_cast<float2 *>(to.prev_position)[row] = ppos;

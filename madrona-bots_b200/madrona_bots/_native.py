@@ -15,7 +15,7 @@ EXPORT = dict(
     PREV_SENSOR_DEPTH=17, STATS=18, PREV_STATS=19, SENSOR_INDEX=20, SPECIES_COUNT=21,
     DEBUG_WORLD_COUNT=100, DEBUG_WORLD_OFFSET=101, DEBUG_RNG_COUNT=102, DEBUG_NUM_FOOD=103,
     DEBUG_FOOD=104, DEBUG_POSE=105, DEBUG_AGENT_HEALTH=106, DEBUG_AGENT_SPECIES=107,
-    DEBUG_AGENT_TARGET=108, DEBUG_ROW_BASE=109,
+    DEBUG_AGENT_TARGET=108, DEBUG_ROW_BASE=109, DEBUG_ROW_OWNER=110,
 )
 
 # every symbol include/mbots.h declares

@@ -6,7 +6,7 @@ import ctypes
 import numpy as np
 import pytest
 
-from parity_util import compare, make_pair
+from parity_util import compare, gpu_np, make_pair
 from test_policy import _make
 
 pytestmark = pytest.mark.gpu
@@ -51,7 +51,13 @@ def test_pack_observations_equals_construct_obs(cuda_device):
         sim.pack_observations(0, A + 1)
 
 
-def _host_sample(shim, weights, seed, draw, row_begin):
+def _agent_ids(sim, start, end, world_id_offset=0):
+    """(GLOBAL world id << 10) | slot of the agents that own rows [start, end) -- what the sampling is keyed on."""
+    o = gpu_np(sim, "DEBUG_ROW_OWNER")[start:end, 0].astype(np.int64) & 0xFFFFFFFF
+    return ((world_id_offset + (o >> 10)) << 10) | (o & 1023)
+
+
+def _host_sample(shim, weights, seed, draw, ids):
     """The kernel's definition, restated on the host with the product's own Threefry (prims shim)."""
     k0, k1, k2 = (ctypes.c_uint32 * 2)(), (ctypes.c_uint32 * 2)(), (ctypes.c_uint32 * 2)()
     shim.shim_init_key(seed, k0)
@@ -59,7 +65,7 @@ def _host_sample(shim, weights, seed, draw, row_begin):
     out = np.empty(len(weights), dtype=np.int32)
     f32 = np.float32
     for r, w in enumerate(weights.astype(np.float32)):
-        shim.shim_split(k1[0], k1[1], row_begin + r, 0, k2)
+        shim.shim_split(k1[0], k1[1], int(ids[r]) & 0xFFFFFFFF, int(ids[r]) >> 32, k2)
         u = f32(shim.shim_sample_uniform(k2[0], k2[1]))
         total = w[0]
         for k in range(1, 6):
@@ -88,7 +94,7 @@ def test_sample_actions_matches_host_restatement(cuda_device):
     w[5] = torch.tensor([0, 0, 0, 0, 0, 1.0])
     before = sim.action_tensor(False).to_torch().clone()
     idx = sim.sample_actions(start, end, w, seed=9, draw=3, want_index=True)
-    want = _host_sample(shim(), w.cpu().numpy(), 9, 3, start)
+    want = _host_sample(shim(), w.cpu().numpy(), 9, 3, _agent_ids(sim, start, end))
     np.testing.assert_array_equal(idx.cpu().numpy(), want)
     act = sim.action_tensor(False).to_torch()
     assert torch.equal(act[start:end], torch.nn.functional.one_hot(idx.long(), 6).to(torch.int32))
@@ -194,7 +200,7 @@ def test_fused_policy_kernel_matches_its_restatement(cuda_device, rtype, acts, l
         # sampling: the kernel's own logits -> softmax weights -> the documented inverse-CDF draw
         l = lg.cpu().numpy().astype(np.float32)
         w = np.exp((l - l.max(axis=1, keepdims=True)).astype(np.float32)).astype(np.float32)
-        want = _host_sample(shim(), w, 5, 8, start)
+        want = _host_sample(shim(), w, 5, 8, _agent_ids(sim, start, end))
         assert int((idx.cpu().numpy() != want).sum()) <= max(1, (end - start) // 500)
         act = sim.action_tensor(False).to_torch()
         assert torch.equal(act[start:end], torch.nn.functional.one_hot(idx.long(), 6).to(torch.int32))
@@ -342,3 +348,31 @@ def test_fused_policy_matches_reference_models_py_on_shipped_weights(cuda_device
         top2 = np.sort(ref, axis=1)[:, -2:]
         clear = (top2[:, 1] - top2[:, 0]) > 2.0 * err.max()       # the preferred action cannot flip where the gap exceeds the error
         assert (lg.argmax(1)[clear] == ref.argmax(1)[clear]).all()
+
+
+def test_sampled_actions_do_not_depend_on_the_sharding(cuda_device):
+    """an agent's draw is keyed on (seed, draw, GLOBAL world id, slot), not on its shard-local row, so worlds
+    [8, 16) simulated alone sample the same actions -- and evolve identically with the policy in the loop -- as inside a
+    16-world handle."""
+    import os
+    import torch
+    from madrona_bots import SimManager
+    from madrona_bots.policy import PolicyRunner, load_universe_fixture
+    path = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "policy_universe_violence.npz")
+    pols = load_universe_fixture(path, "cuda:0")
+    full = SimManager(0, 16, 21, 32)
+    part = SimManager(0, 8, 21, 32, world_id_offset=8)
+    runners = [PolicyRunner(full, pols, seed=3, fused="sw128"), PolicyRunner(part, pols, seed=3, fused="sw128")]
+    for t in range(25):
+        for sim, run in zip((full, part), runners):
+            sim.step()
+            run.act()
+            sim.shift_observations()
+    for sim in (full, part):
+        sim.step()
+    off = int(gpu_np(full, "DEBUG_WORLD_OFFSET")[8, 0])
+    np.testing.assert_array_equal(gpu_np(full, "DEBUG_WORLD_COUNT")[8:], gpu_np(part, "DEBUG_WORLD_COUNT"))
+    np.testing.assert_array_equal(gpu_np(full, "DEBUG_POSE")[off:], gpu_np(part, "DEBUG_POSE"))
+    np.testing.assert_array_equal(gpu_np(full, "DEBUG_AGENT_HEALTH")[off:], gpu_np(part, "DEBUG_AGENT_HEALTH"))
+    st = part.episode_stats()
+    assert st[10] > 0 or st[11] > 0 or st[15] > 0, "the policy must have done something"
