@@ -283,7 +283,7 @@ def test_fused_policy_many_tiles_per_cta(cuda_device, layout):
     w = np.exp((l - l.max(axis=1, keepdims=True)).astype(np.float32)).astype(np.float32)
     got = idx.cpu().numpy()
     for lo, hi in ((0, 20000), (A - 20000, A)):               # the host restatement is a Python loop: two slices
-        want = _host_sample(shim(), w[lo:hi], 2, 3, lo)
+        want = _host_sample(shim(), w[lo:hi], 2, 3, _agent_ids(sim, lo, hi))
         assert int((got[lo:hi] != want).sum()) <= (hi - lo) // 500
     act = sim.action_tensor(False).to_torch()
     assert torch.equal(act, torch.nn.functional.one_hot(idx.long(), 6).to(torch.int32))
