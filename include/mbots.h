@@ -133,6 +133,8 @@ int mbots_sync(mbots_sim *sim, void *stream);
  *   actions_dev  device pointer to (action_rows, 6) int32 rows in observation-row order, or NULL to leave the
  *                action export as the caller wrote it through its view. min(live agents, action_rows) rows are
  *                written; the live count is read ON THE DEVICE, so the host may enqueue steps without knowing it.
+ *                The matrix is read when the step RUNS, not when it is enqueued: keep it alive and unchanged until then
+ *                (mbots_sync, or an event of the caller's recorded behind the call).
  *   shift        non-zero: Manager::shiftObservations of the new rows follows the step.
  * Nothing is waited for. Several steps may be in flight (the host runs ahead of the device); launch geometry is
  * then sized from the newest population that has reached the host plus slack, and worlds that outgrow it take the

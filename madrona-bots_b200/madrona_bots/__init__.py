@@ -118,7 +118,8 @@ class SimManager:
     def rollout_step_async(self, actions=None, shift=True):
         """One launch: [write `actions` (a contiguous CUDA int32 (rows, 6) tensor in observation-row order; only the live
         rows are written, the count is read on the device)] -> step + sensor -> [shift_observations]. Nothing is waited
-        for: the host may enqueue the next step at once (`sync()` waits for the last one)."""
+        for: the host may enqueue the next step at once (`sync()` waits for the last one). `actions` is read when the
+        step runs on the device: keep the tensor alive and unchanged until then."""
         ptr, rows = None, 0
         if actions is not None:
             assert actions.is_cuda and actions.is_contiguous() and actions.dim() == 2 and actions.shape[1] == 6
