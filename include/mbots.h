@@ -173,6 +173,12 @@ int mbots_num_agents(mbots_sim *sim, uint32_t *out);
  * pointer, dims and dtype of one export. `id` is an mbots_export_id. */
 int mbots_tensor(mbots_sim *sim, int32_t id, void **dev_ptr, int64_t dims[2], int32_t *dtype);
 
+/* First row of every species block of the current exports, and the total: out[k] .. out[k + 1] are the rows of species
+ * k + 1 (rows are species-major, src/sim/sim.cpp:1148-1149). Exact -- the cumulative sum of species_count_tensor the
+ * reference's loop uses (learn/training_loop.py:43-45) is taken before the step's respawns -- and free: the totals
+ * arrive on the host with every step. MBOTS_ESTATE while asynchronous steps are pending. */
+int mbots_species_blocks(mbots_sim *sim, uint32_t out[5]);
+
 /* Rows every agent-indexed export is allocated for (num_worlds x per-world capacity): the buffers behind
  * mbots_tensor() stay valid, at fixed addresses, for this many rows, so a binding may build one view per
  * export and re-slice it to the live count after each step instead of re-wrapping the pointer. */

@@ -547,6 +547,16 @@ int mbots_num_agents(mbots_sim *s, uint32_t *out)
     return MBOTS_OK;
 }
 
+int mbots_species_blocks(mbots_sim *s, uint32_t out[5])
+{
+    if (!s || !out) return fail(MBOTS_EINVAL, "null argument");
+    if (s->dirty) return fail(MBOTS_ESTATE, "asynchronous work pending: call mbots_sync first");
+    uint32_t a = 0;
+    for (int k = 0; k < 4; ++k) { out[k] = a; a += s->hTotals->speciesTotal[k]; }
+    out[4] = a;
+    return MBOTS_OK;
+}
+
 int mbots_row_capacity(mbots_sim *s, uint64_t *out)
 {
     if (!s || !out) return fail(MBOTS_EINVAL, "null argument");

@@ -265,10 +265,9 @@ class SimManager:
         """[(start, end)] * 4: the row range of every species in the current exports (rows are species-major,
         src/sim/sim.cpp:1148-1149). Exact, unlike the cumulative sum of `species_count_tensor` the reference's loop
         uses (learn/training_loop.py:43-45): those counts are taken before the step's respawns (sim.cpp:804-836)."""
-        A = self.num_agents()
-        base = self.export("DEBUG_ROW_BASE").to_torch()[0].tolist()      # first row of (world 0, species k)
-        starts = [int(b) for b in base] + [A]
-        return [(starts[k], starts[k + 1]) for k in range(4)]
+        out = (ctypes.c_uint32 * 5)()                    # from the totals every step brings to the host: no device read
+        _native.check(self._lib.mbots_species_blocks(self._h, out), "mbots_species_blocks")
+        return [(int(out[k]), int(out[k + 1])) for k in range(4)]
 
     def sample_actions(self, start, end, weights, seed, draw, want_index=False):
         """Categorical sample of rows [start, end) from (n, 6) float32 action weights + one-hot write into

@@ -160,6 +160,12 @@ def test_species_blocks_are_contiguous(cuda_device):
     assert np.array_equal(np.sort(rows), np.arange(len(rows)))
     assert np.all(np.diff(species[order]) >= 0), "rows must be species-major"
     assert rb[0, 0] == 0
+    # SimManager.species_blocks(): the exact row range of every species, from the totals the step brought to the host
+    blocks = g.species_blocks()
+    assert [b[0] for b in blocks] == [int(x) for x in rb[0]] and blocks[3][1] == g.num_agents()
+    by_row = species[order]
+    for k, (a, b) in enumerate(blocks):
+        assert (by_row[a:b] == k + 1).all() and b - a == int((species == k + 1).sum())
 
 
 class _GpuAdapter:
