@@ -1,23 +1,23 @@
-/* sim_kernels.cu -- the per-step hot path of madrona-bots as four sm_100a kernels.
+/* sim_kernels.cu -- the per-step hot path of madrona-bots as hand-written sm_100a kernels.
  *
- *   step_kernel    one CTA per world, one thread per agent slot. Restates the Step task
- *                  graph up to the world sort (src/sim/sim.cpp:1061-1132): chunk reset,
- *                  food spawn, actionSystem, healthSync, surroundings, species tracker,
- *                  speciesInfoSync + respawn, and the compaction the reference gets from
- *                  SortArchetypeNode<Agent, WorldID>. World state lives in shared memory
- *                  for the duration; every cross-agent effect (shots, chunk counters,
- *                  food, births) is a shared-memory atomic or a block scan.
- *   scan_kernel    the only cross-world dependency: exclusive scan of the per-(world,
- *                  species) row counts in species-major order -> first row of each
- *                  (world, species) segment. Replaces the global radix sort by
- *                  SpeciesObservation (src/sim/sim.cpp:1148-1149).
- *   export_kernel  one CTA per world. Gathers every column that travels with an agent from
- *                  its old row to its new row (the "sort"), writes the observation exports
- *                  (updateObservations :687-717, updateSensorOutputIdx :736-789, rewardSystem
- *                  :840-983) and runs the 32-ray sensor over the world's agents staged in
- *                  shared memory (M/src/mw/device/bvh_raycast.cpp:193-305; exhaustive nearest
- *                  hit instead of a TLAS).
- *   shift_kernel   shiftObservationsSystem + shiftHiddenState (src/sim/sim.cpp:1002-1048).
+ *   step_kernel        one WARP per world (four worlds per CTA, no block barriers). Restates the Step task graph up to
+ *                      the world sort (src/sim/sim.cpp:1061-1132): chunk reset, food spawn, actionSystem, healthSync,
+ *                      surroundings, species tracker, speciesInfoSync + respawn, and the compaction the reference gets
+ *                      from SortArchetypeNode<Agent, WorldID>. World state lives in the warp's shared memory for the
+ *                      duration; every cross-agent effect (shots, chunk counters, food, births) is a shared-memory
+ *                      atomic, a ballot + popc rank or a warp reduction. Actions come from the action export or straight
+ *                      from the caller's device matrix (StepOpts).
+ *   scan_fused_kernel  the only cross-world dependency: exclusive scan of the per-(world, species) row counts in
+ *                      species-major order -> first row of each (world, species) segment. Replaces the global radix
+ *                      sort by SpeciesObservation (src/sim/sim.cpp:1148-1149). One launch with a grid barrier
+ *                      (tile_sum_kernel + scan_kernel when the grid cannot be resident at once).
+ *   export_kernel      one warp per world (or 2-8 single-warp CTAs per world for small launches). Gathers every column
+ *                      that travels with an agent from its old row to its new row (the "sort"), writes the observation
+ *                      exports (updateObservations :687-717, updateSensorOutputIdx :736-789, rewardSystem :840-983) and
+ *                      runs the 32-ray sensor over the world's agents staged in shared memory
+ *                      (M/src/mw/device/bvh_raycast.cpp:193-305; two-stage angular cull + exact ray / sphere tests instead
+ *                      of a TLAS). With StepOpts::fuseShift it also leaves prev := cur, i.e. the shift.
+ *   shift_kernel       shiftObservationsSystem + shiftHiddenState (src/sim/sim.cpp:1002-1048) as a call of its own.
  *
  * Compiled with -fmad=false: results must be bit-identical to the CPU oracle.
  */
