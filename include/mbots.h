@@ -254,6 +254,33 @@ int mbots_policy_act(mbots_sim *sim, uint32_t row_begin, uint32_t row_end, const
                      const mbots_policy_program *program, uint32_t seed, uint32_t draw, int32_t sample,
                      float *out_logits, int32_t *out_index, void *stream);
 
+/* NO COUNTERPART IN THE REFERENCE -- added for callers that cannot call
+ * cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
+ *
+ * The step's row scan (what orders the observation rows species-major, src/sim/sim.cpp:1148-1149) as a stand-alone
+ * call that ALLOCATES NOTHING: no cudaMalloc / cudaFree / allocating library routine, no handle. Its scratch memory
+ * (one 32-byte record per tile of 1,024 worlds) is a file-scope __device__ array of the library, 8 KiB, held by every
+ * GPU that loads the library until exit -- hence the limit num_worlds <= MBOTS_ROW_SCAN_STATIC_MAX_WORLDS; more is
+ * rejected with MBOTS_EINVAL and a message (use a simulator handle for larger populations).
+ *
+ *   species_rows  in   device int32 (num_worlds, 4): rows of (world, species k + 1); 16-byte aligned
+ *   row_base      out  device int32 (num_worlds, 4): first row of (world, species) when rows are ordered
+ *                      (species, world): rows of earlier species in all worlds + rows of this species in earlier
+ *                      worlds -- what MBOTS_DEBUG_ROW_BASE shows of a handle; 16-byte aligned
+ *   world_offset  out  device int32 (num_worlds) or NULL: exclusive scan of the per-world sums
+ *                      (Manager::agentWorldOffsets; MBOTS_DEBUG_WORLD_OFFSET of a handle)
+ *   totals        out  device uint32 (6) or NULL: rows per species [0..3], all rows [4], largest world [5]
+ *
+ * Sums are int32: the total must stay below 2^31. All buffers must be device memory of ONE GPU (the call makes that
+ * GPU current for its duration); `stream` must belong to it. Asynchronous on `stream`: two kernel launches.
+ * Every call on a GPU shares the one scratch array, which keeps the last call's contents; nothing in it needs to
+ * start at zero (each call overwrites what it reads), but calls that OVERLAP on the GPU (different streams, no
+ * dependency) race on it -- serialise them. The first call on a GPU looks up the array's device address
+ * (cudaGetSymbolAddress); make that call outside stream capture. */
+#define MBOTS_ROW_SCAN_STATIC_MAX_WORLDS 262144u
+int mbots_row_scan_static(const int32_t *species_rows, uint32_t num_worlds, int32_t *row_base, int32_t *world_offset,
+                          uint32_t *totals, void *stream);
+
 const char *mbots_last_error(void);
 const char *mbots_version(void);
 

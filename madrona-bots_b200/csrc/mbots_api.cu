@@ -32,6 +32,9 @@ static int fail(int code, const char *what, cudaError_t ce = cudaSuccess)
     return code;
 }
 
+/* row_scan_static.cu reports through the same mbots_last_error() */
+namespace mbk { int set_error(int code, const char *what, cudaError_t ce) { return fail(code, what, ce); } }
+
 #define CU(call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) return fail(MBOTS_ECUDA, #call, e_); } while (0)
 
 enum { K_STEP = 0, K_SCAN = 1, K_EXPORT = 2, K_SHIFT = 3, K_COUNT = 4 };

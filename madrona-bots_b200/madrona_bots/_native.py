@@ -26,7 +26,7 @@ SYMBOLS = [
     "mbots_episode_stats", "mbots_launch_count", "mbots_profile", "mbots_profile_read",
     "mbots_row_capacity", "mbots_pack_observations", "mbots_sample_actions", "mbots_policy_act", "mbots_state_bytes", "mbots_save_state", "mbots_load_state",
     "mbots_rollout_step_async", "mbots_write_actions", "mbots_graph_launch_count", "mbots_debug_stale_views", "mbots_species_blocks",
-    "mbots_last_error", "mbots_version",
+    "mbots_row_scan_static", "mbots_last_error", "mbots_version",
 ]
 
 
@@ -74,6 +74,7 @@ def lib():
     L.mbots_graph_launch_count.argtypes = [vp, ctypes.POINTER(u64)]
     L.mbots_debug_stale_views.argtypes = [vp, i32]
     L.mbots_species_blocks.argtypes = [vp, ctypes.POINTER(u32)]
+    L.mbots_row_scan_static.argtypes = [vp, u32, vp, vp, vp, vp]
     L.mbots_num_agents.argtypes = [vp, ctypes.POINTER(u32)]
     L.mbots_tensor.argtypes = [vp, i32, ctypes.POINTER(vp), ctypes.POINTER(ctypes.c_int64), ctypes.POINTER(i32)]
     L.mbots_set_action.argtypes = [vp, u32, i32, i32, i32, i32, i32, i32]
