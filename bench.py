@@ -415,8 +415,46 @@ def policy_leg(args, sim, leg, dev, world, idx):
     except Exception:
         tf_peak, tf_src = 1400.0, "fallback"
     tflops = tot[2] * 1e6 / (t_pol_max * 1e-3) / 1e12 / world          # per GPU
+
+    # the same loop with nothing waited for: the acting kernels take their row ranges from the device
+    # (mbots_policy_act_species), the step is the one-launch rollout step with the shift fused, the host runs ahead
+    def run_async(n):
+        inflight = []
+        for _ in range(n):
+            runner.act_async()
+            sim.rollout_step_async(None, shift=True)
+            e = torch.cuda.Event()
+            e.record()
+            inflight.append(e)
+            if len(inflight) > RUN_AHEAD:
+                inflight.pop(0).synchronize()
+        sim.sync()
+
+    run_async(args.warmup)
+    a_ms, a_agents = [], 0
+    for _ in range(5):
+        st0 = sim.episode_stats()[0]
+        if world > 1:
+            import torch.distributed as dist
+            dist.barrier()
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        run_async(args.steps)
+        e1.record()
+        torch.cuda.synchronize()
+        a_ms.append(allreduce_max(e0.elapsed_time(e1), device=dev))
+        # agents acted on = the populations BEFORE each of the K steps (agent_steps counts them after)
+        a_agents = sim.episode_stats()[0] - st0
+    a_ms.sort()
+    a_med = a_ms[len(a_ms) // 2]
+    a_tot = allreduce_stats([a_agents, 0], device=dev)[0]
     return {"value": tot[0] / (t_all_max * 1e-3), "unit": UNIT, "ms_per_step": t_all_max / args.steps,
             "policy_ms_per_step": t_pol_max / args.steps, "steps": args.steps,
+            "async": {"value": a_tot / (a_med * 1e-3), "unit": UNIT, "ms_per_step": a_med / args.steps,
+                      "launches_per_step": 5, "run_ahead_steps": RUN_AHEAD,
+                      "what": "act_async (4 acting kernels, row ranges resolved on the device) + rollout_step_async(shift): "
+                              "the same work with no host wait, host up to 3 steps ahead; median of 5 regions of K steps"},
             "what": "step() + 4 fused acting kernels (tcgen05, bf16 in / fp32 accumulate) + shift_observations per step; "
                     "the host waits for every step (the species row ranges come from it)",
             "weights": "checkpoints/universe_violence latest_model_epoch_788 (GRU, LSTM, RNN, RNN), fixture npz",

@@ -254,6 +254,16 @@ int mbots_policy_act(mbots_sim *sim, uint32_t row_begin, uint32_t row_end, const
                      const mbots_policy_program *program, uint32_t seed, uint32_t draw, int32_t sample,
                      float *out_logits, int32_t *out_index, void *stream);
 
+/* The same kernel for the whole block of ONE species (0..3) of the current row set, with the row range resolved ON THE
+ * DEVICE from the totals the last step's row scan wrote: the host needs neither mbots_species_blocks() nor a wait for the
+ * step, so a rollout with the policy in the loop -- learn/training_loop.py:36-83,135-137: act, step, shift -- can be
+ * enqueued several steps ahead (mbots_rollout_step_async with actions = NULL reads the rows this call wrote). Valid while
+ * asynchronous steps are pending. MBOTS_LAYOUT_SW128 programs only. out_logits (rows, 6) / out_index (rows) are indexed by
+ * OBSERVATION ROW here (size them for mbots_row_capacity or the population bound you keep), not by row within the block. */
+int mbots_policy_act_species(mbots_sim *sim, int32_t species, const void *blob, uint64_t blob_bytes,
+                             const mbots_policy_program *program, uint32_t seed, uint32_t draw, int32_t sample,
+                             float *out_logits, int32_t *out_index, void *stream);
+
 /* NO COUNTERPART IN THE REFERENCE -- added for callers that cannot call
  * cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
  *

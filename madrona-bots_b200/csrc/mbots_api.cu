@@ -906,6 +906,29 @@ const char *launch_policy_umma(const ObsSet &o, uint32_t row_begin, uint32_t row
                                float *out_logits, int32_t *out_index, cudaStream_t s);
 }
 
+namespace mbk {
+const char *launch_policy_umma_species(const ObsSet &o, const Totals *totals, int species, const void *blob, uint64_t blob_bytes,
+                                       const mbots_policy_program &prog, uint32_t seed, uint32_t draw, int do_sample,
+                                       float *out_logits, int32_t *out_index, cudaStream_t s);
+}
+
+extern "C" int mbots_policy_act_species(mbots_sim *s, int32_t species, const void *blob, uint64_t blob_bytes,
+                                        const mbots_policy_program *program, uint32_t seed, uint32_t draw, int32_t sample,
+                                        float *out_logits, int32_t *out_index, void *stream)
+{
+    if (!s || !blob || !program) return fail(MBOTS_EINVAL, "null argument");
+    if (species < 0 || species > 3) return fail(MBOTS_EINVAL, "species must be 0..3");
+    if (program->layout != MBOTS_LAYOUT_SW128)
+        return fail(MBOTS_EINVAL, "mbots_policy_act_species takes MBOTS_LAYOUT_SW128 programs only");
+    DeviceGuard g(s->device);
+    const char *err = launch_policy_umma_species(s->d.obs[s->cur], s->d.totals, species, blob, blob_bytes, *program, seed, draw,
+                                                 sample != 0, out_logits, out_index, (cudaStream_t)stream);
+    if (err) return fail(MBOTS_EINVAL, err);
+    CU(cudaGetLastError());
+    s->launches += 1;
+    return MBOTS_OK;
+}
+
 extern "C" int mbots_policy_act(mbots_sim *s, uint32_t row_begin, uint32_t row_end, const void *blob, uint64_t blob_bytes,
                                 const mbots_policy_program *program, uint32_t seed, uint32_t draw, int32_t sample,
                                 float *out_logits, int32_t *out_index, void *stream)

@@ -283,8 +283,18 @@ struct UObsPtrs { const uint8_t *depth; const float *health; const float *positi
 __global__ void __launch_bounds__(kUThreads, 1)     /* 17 warps are allocated as 20: 96 registers per thread is the ceiling */
 policy_umma_kernel(UObsPtrs o, int32_t *__restrict__ action, uint32_t row_begin, uint32_t rows, const unsigned char *__restrict__ blob,
                    mbots_policy_program prog, UmmaPlan plan, uint32_t seed, uint32_t draw, int do_sample,
-                   float *__restrict__ out_logits, int32_t *__restrict__ out_index)
+                   float *__restrict__ out_logits, int32_t *__restrict__ out_index, const Totals *__restrict__ totals, int species)
 {
+    /* totals != NULL: the rows are the block of `species` in the current row set, resolved HERE from what the last step's
+     * row scan wrote -- the host neither knows nor waits for the population; out_logits / out_index are then indexed by
+     * observation row, not by row within the block */
+    if (totals != nullptr) {
+        row_begin = 0;
+        for (int k = 0; k < species; ++k) row_begin += totals->speciesTotal[k];
+        rows = totals->speciesTotal[species];
+        if (out_logits) out_logits += (size_t)row_begin * 6;
+        if (out_index) out_index += row_begin;
+    }
     extern __shared__ unsigned char smem_raw[];
     unsigned char *smem = reinterpret_cast<unsigned char *>((reinterpret_cast<uintptr_t>(smem_raw) + 1023u) & ~(uintptr_t)1023u);
     const uint32_t smem_base = (uint32_t)__cvta_generic_to_shared(smem);
@@ -524,13 +534,13 @@ static const char *policy_umma_plan(const mbots_policy_program &p, uint64_t blob
     return nullptr;
 }
 
-const char *launch_policy_umma(const ObsSet &o, uint32_t row_begin, uint32_t rows, const void *blob, uint64_t blob_bytes,
-                               const mbots_policy_program &prog, uint32_t seed, uint32_t draw, int do_sample,
+static const char *launch_umma(const ObsSet &o, const Totals *totals, int species, uint32_t row_begin, uint32_t rows, const void *blob,
+                               uint64_t blob_bytes, const mbots_policy_program &prog, uint32_t seed, uint32_t draw, int do_sample,
                                float *out_logits, int32_t *out_index, cudaStream_t s)
 {
     UmmaPlan plan = {};
     const char *err = policy_umma_plan(prog, blob_bytes, plan);
-    if (err || rows == 0) return err;
+    if (err || (rows == 0 && totals == nullptr)) return err;
     if (reinterpret_cast<uintptr_t>(blob) & 15u) return "the blob must be 16-byte aligned";
     int dev = 0, sms = 148;
     cudaGetDevice(&dev);
@@ -542,11 +552,27 @@ const char *launch_policy_umma(const ObsSet &o, uint32_t row_begin, uint32_t row
     }
     const uint32_t pairs = ((rows + kUTile - 1) / kUTile + 1) / 2;
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-    const uint32_t grid = pairs < (uint32_t)sms ? pairs : (uint32_t)sms;      /* persistent: one CTA per SM */
+    /* persistent: one CTA per SM (all of them when the row count is only known on the device) */
+    const uint32_t grid = totals == nullptr && pairs < (uint32_t)sms ? pairs : (uint32_t)sms;
     const UObsPtrs ptrs = {o.depth, o.health, o.position, o.semantic, o.surrounding, o.owner, o.worldIdOffset};
     policy_umma_kernel<<<grid, kUThreads, kUSmemBytes, s>>>(ptrs, o.action, row_begin, rows, static_cast<const unsigned char *>(blob),
-                                                            prog, plan, seed, draw, do_sample, out_logits, out_index);
+                                                            prog, plan, seed, draw, do_sample, out_logits, out_index, totals, species);
     return nullptr;
+}
+
+const char *launch_policy_umma(const ObsSet &o, uint32_t row_begin, uint32_t rows, const void *blob, uint64_t blob_bytes,
+                               const mbots_policy_program &prog, uint32_t seed, uint32_t draw, int do_sample,
+                               float *out_logits, int32_t *out_index, cudaStream_t s)
+{
+    return launch_umma(o, nullptr, 0, row_begin, rows, blob, blob_bytes, prog, seed, draw, do_sample, out_logits, out_index, s);
+}
+
+/* the block of one species (0..3) of the current row set, row range resolved on the device from `totals` */
+const char *launch_policy_umma_species(const ObsSet &o, const Totals *totals, int species, const void *blob, uint64_t blob_bytes,
+                                       const mbots_policy_program &prog, uint32_t seed, uint32_t draw, int do_sample,
+                                       float *out_logits, int32_t *out_index, cudaStream_t s)
+{
+    return launch_umma(o, totals, species, 0, 0, blob, blob_bytes, prog, seed, draw, do_sample, out_logits, out_index, s);
 }
 
 } // namespace mbk

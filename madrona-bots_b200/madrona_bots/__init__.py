@@ -299,6 +299,17 @@ class SimManager:
             return idx, lg
         return idx if want_index else lg
 
+    def policy_act_species(self, species, fused, seed, draw, sample=True, out_index=None, out_logits=None):
+        """`policy_act` for the whole block of one species (0..3), its row range resolved on the device: no host wait for
+        the last step, valid while asynchronous steps are pending. `out_index` (rows,) int32 / `out_logits` (rows, 6)
+        float32: optional caller-owned CUDA tensors indexed by observation row (size them for the population bound)."""
+        _native.check(self._lib.mbots_policy_act_species(
+            self._h, int(species), ctypes.c_void_p(fused.blob.data_ptr()), fused.blob.numel(), ctypes.byref(fused.program),
+            int(seed) & 0xFFFFFFFF, int(draw) & 0xFFFFFFFF, 1 if sample else 0,
+            ctypes.c_void_p(out_logits.data_ptr()) if out_logits is not None else None,
+            ctypes.c_void_p(out_index.data_ptr()) if out_index is not None else None, self._stream()),
+            "mbots_policy_act_species")
+
     # ---- state checkpoint / restore (SURVEY section 8(f) item 3) ---------------------------
     def save_state(self, path=None):
         """Every persistent array of the simulator as one uint8 numpy blob (also written to `path`

@@ -334,3 +334,13 @@ class PolicyRunner:
             picked.append(self.sim.sample_actions(start, end, weights, self.seed, self.draw, want_index=want_index))
         self.draw += 1
         return picked
+
+    def act_async(self, out_index=None, out_logits=None):
+        """act() without any host wait: four kernels whose row ranges are resolved on the device (fused SW128 policies
+        only). With `sim.rollout_step_async(None, shift=True)` after it, a whole rollout step -- act, step, sensor, shift
+        -- is five launches and the host may run several steps ahead; same draws as act(), so the same rollout."""
+        if self.fused is None:
+            raise ValueError("act_async needs fused policies (PolicyRunner(..., fused='sw128'))")
+        for k in range(4):
+            self.sim.policy_act_species(k, self.fused[k], self.seed, self.draw, out_index=out_index, out_logits=out_logits)
+        self.draw += 1

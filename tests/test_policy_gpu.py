@@ -376,3 +376,50 @@ def test_sampled_actions_do_not_depend_on_the_sharding(cuda_device):
     np.testing.assert_array_equal(gpu_np(full, "DEBUG_AGENT_HEALTH")[off:], gpu_np(part, "DEBUG_AGENT_HEALTH"))
     st = part.episode_stats()
     assert st[10] > 0 or st[11] > 0 or st[15] > 0, "the policy must have done something"
+
+
+def test_act_async_rollout_equals_the_blocking_loop(cuda_device):
+    """mbots_policy_act_species: the acting kernels take their row ranges from the device, so act + step + sensor + shift
+    can be enqueued steps ahead with no host wait. Same draws, same rows: the rollout must equal the blocking loop
+    (step, act through species_blocks(), shift) on every export, and the indices / logits it reports (by observation row)
+    must be the blocking call's."""
+    import os
+    import torch
+    from madrona_bots import SimManager
+    from madrona_bots.policy import PolicyRunner, load_universe_fixture
+    from parity_util import ROW_EXPORTS, WORLD_EXPORTS, AGENT_DEBUG
+    path = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "policy_universe_violence.npz")
+    pols = load_universe_fixture(path, "cuda:0")
+    a, b = SimManager(0, 300, 5, 32), SimManager(0, 300, 5, 32)
+    ra, rb = PolicyRunner(a, pols, seed=9, fused="sw128"), PolicyRunner(b, pols, seed=9, fused="sw128")
+    cap = 300 * 64
+    idx = torch.full((cap,), -1, dtype=torch.int32, device="cuda:0")
+    lg = torch.zeros((cap, 6), dtype=torch.float32, device="cuda:0")
+    a.step(); b.step()
+    a.shift_observations(); b.shift_observations()
+    steps = 24
+    for t in range(steps):
+        picked = ra.act(want_index=True)            # blocking cadence: the host knows the row ranges
+        a.step()
+        a.shift_observations()
+        last = t == steps - 1
+        rb.act_async(out_index=idx if last else None, out_logits=lg if last else None)   # nothing waits for anything
+        b.rollout_step_async(None, shift=True)
+        if last:
+            b.sync()
+            n_before = sum(int(p.numel()) for p in picked if p is not None)
+            want = torch.cat([p for p in picked if p is not None]).cpu().numpy()
+            np.testing.assert_array_equal(idx[:n_before].cpu().numpy(), want)
+            assert bool((idx[n_before:] == -1).all()), "wrote index rows beyond the population"
+            assert bool(lg[:n_before].abs().sum(dim=1).gt(0).all()) and not bool(lg[n_before:].any())
+    b.sync()
+    assert a.num_agents() == b.num_agents()
+    for name in WORLD_EXPORTS + AGENT_DEBUG + ROW_EXPORTS + ["DEBUG_FOOD"]:
+        np.testing.assert_array_equal(gpu_np(a, name), gpu_np(b, name), err_msg=name)
+    st = b.episode_stats()
+    assert st == a.episode_stats() and (st[10] > 0 or st[11] > 0 or st[15] > 0), "the policy must have done something"
+    with pytest.raises(RuntimeError, match="SW128"):
+        from madrona_bots.policy import FusedPolicy
+        b.policy_act_species(0, FusedPolicy(pols[0], "rowpad"), 0, 0)
+    with pytest.raises(RuntimeError, match="species must be"):
+        b.policy_act_species(4, rb.fused[0], 0, 0)
