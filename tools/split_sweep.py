@@ -20,6 +20,7 @@ def main():
     W = int(sys.argv[1])
     steps = int(sys.argv[2]) if len(sys.argv) > 2 else 50
     prewarm = int(os.environ.get("SWEEP_PREWARM", "10"))
+    use_events = os.environ.get("SWEEP_EVENTS", "1") != "0"     # a torch event per step bounds the host's run-ahead
     dev = torch.device("cuda", 0)
     sim = SimManager(0, W, bench.SEED, bench.INIT_AGENTS)
     rows_cap = W * 48
@@ -38,11 +39,12 @@ def main():
         for _ in range(steps):
             sim.rollout_step_async(pool[idx % bench.POOL], shift=True)
             idx += 1
-            ev = torch.cuda.Event()
-            ev.record()
-            inflight.append(ev)
-            if len(inflight) > bench.RUN_AHEAD:
-                inflight.pop(0).synchronize()
+            if use_events:
+                ev = torch.cuda.Event()
+                ev.record()
+                inflight.append(ev)
+                if len(inflight) > bench.RUN_AHEAD:
+                    inflight.pop(0).synchronize()
         e1.record()
         sim.sync()
         torch.cuda.synchronize()
@@ -57,7 +59,7 @@ def main():
     counts = sim.export("DEBUG_WORLD_COUNT").to_torch().float()
     print(json.dumps({
         "worlds": W, "split_log2": os.environ.get("MBOTS_EXPORT_SPLIT_LOG2", "default"),
-        "heavy64": os.environ.get("MBOTS_EXPORT_SPLIT_HEAVY64", "default"),
+        "graphs": os.environ.get("MBOTS_GRAPHS", "1"), "events": use_events,
         "ms_per_step": round(statistics.median(times), 5), "ms_min": round(min(times), 5),
         "kernels_ms": {k: round(v["ms"], 5) for k, v in prof.items()},
         "agents": sim.num_agents(), "n_mean": round(float(counts.mean()), 2), "n_std": round(float(counts.std()), 2),
