@@ -452,9 +452,10 @@ def policy_leg(args, sim, leg, dev, world, idx):
     return {"value": tot[0] / (t_all_max * 1e-3), "unit": UNIT, "ms_per_step": t_all_max / args.steps,
             "policy_ms_per_step": t_pol_max / args.steps, "steps": args.steps,
             "async": {"value": a_tot / (a_med * 1e-3), "unit": UNIT, "ms_per_step": a_med / args.steps,
-                      "launches_per_step": 5, "run_ahead_steps": RUN_AHEAD,
-                      "what": "act_async (4 acting kernels, row ranges resolved on the device) + rollout_step_async(shift): "
-                              "the same work with no host wait, host up to 3 steps ahead; median of 5 regions of K steps"},
+                      "launches_per_step": 2, "run_ahead_steps": RUN_AHEAD,
+                      "what": "act_async (ONE acting kernel for the four species, row ranges resolved on the device) + "
+                              "rollout_step_async(shift) (one graph launch): the same work with no host wait, host up to 3 steps "
+                              "ahead; median of 5 regions of K steps"},
             "what": "step() + 4 fused acting kernels (tcgen05, bf16 in / fp32 accumulate) + shift_observations per step; "
                     "the host waits for every step (the species row ranges come from it)",
             "weights": "checkpoints/universe_violence latest_model_epoch_788 (GRU, LSTM, RNN, RNN), fixture npz",

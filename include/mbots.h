@@ -264,6 +264,15 @@ int mbots_policy_act_species(mbots_sim *sim, int32_t species, const void *blob, 
                              const mbots_policy_program *program, uint32_t seed, uint32_t draw, int32_t sample,
                              float *out_logits, int32_t *out_index, void *stream);
 
+/* All four species in ONE launch of that kernel (network k acts on the block of species k + 1; row ranges resolved on the
+ * device as above): the persistent CTAs walk the tiles of all four blocks in one pass, so the launch ramps up and drains once
+ * instead of four times -- what matters when a GPU holds few worlds. Same draws and results as four
+ * mbots_policy_act_species calls. MBOTS_EINVAL if the four networks' bias vectors together exceed the kernel's shared-memory
+ * copy (6,144 floats): use the per-species call then. */
+int mbots_policy_act_all(mbots_sim *sim, const void *const blobs[4], const uint64_t blob_bytes[4],
+                         const mbots_policy_program *const programs[4], uint32_t seed, uint32_t draw, int32_t sample,
+                         float *out_logits, int32_t *out_index, void *stream);
+
 /* NO COUNTERPART IN THE REFERENCE -- added for callers that cannot call
  * cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
  *

@@ -907,9 +907,27 @@ const char *launch_policy_umma(const ObsSet &o, uint32_t row_begin, uint32_t row
 }
 
 namespace mbk {
-const char *launch_policy_umma_species(const ObsSet &o, const Totals *totals, int species, const void *blob, uint64_t blob_bytes,
-                                       const mbots_policy_program &prog, uint32_t seed, uint32_t draw, int do_sample,
-                                       float *out_logits, int32_t *out_index, cudaStream_t s);
+const char *launch_policy_umma_species(const ObsSet &o, const Totals *totals, int species0, int n, const void *const *blobs,
+                                       const uint64_t *blob_bytes, const mbots_policy_program *const *progs, uint32_t seed,
+                                       uint32_t draw, int do_sample, float *out_logits, int32_t *out_index, cudaStream_t s);
+}
+
+static int policy_act_device_rows(mbots_sim *s, int species0, int n, const void *const *blobs, const uint64_t *blob_bytes,
+                                  const mbots_policy_program *const *programs, uint32_t seed, uint32_t draw, int32_t sample,
+                                  float *out_logits, int32_t *out_index, void *stream)
+{
+    for (int k = 0; k < n; ++k) {
+        if (!blobs[k] || !programs[k]) return fail(MBOTS_EINVAL, "null argument");
+        if (programs[k]->layout != MBOTS_LAYOUT_SW128)
+            return fail(MBOTS_EINVAL, "device-resolved row ranges take MBOTS_LAYOUT_SW128 programs only");
+    }
+    DeviceGuard g(s->device);
+    const char *err = launch_policy_umma_species(s->d.obs[s->cur], s->d.totals, species0, n, blobs, blob_bytes, programs, seed, draw,
+                                                 sample != 0, out_logits, out_index, (cudaStream_t)stream);
+    if (err) return fail(MBOTS_EINVAL, err);
+    CU(cudaGetLastError());
+    s->launches += 1;
+    return MBOTS_OK;
 }
 
 extern "C" int mbots_policy_act_species(mbots_sim *s, int32_t species, const void *blob, uint64_t blob_bytes,
@@ -918,15 +936,15 @@ extern "C" int mbots_policy_act_species(mbots_sim *s, int32_t species, const voi
 {
     if (!s || !blob || !program) return fail(MBOTS_EINVAL, "null argument");
     if (species < 0 || species > 3) return fail(MBOTS_EINVAL, "species must be 0..3");
-    if (program->layout != MBOTS_LAYOUT_SW128)
-        return fail(MBOTS_EINVAL, "mbots_policy_act_species takes MBOTS_LAYOUT_SW128 programs only");
-    DeviceGuard g(s->device);
-    const char *err = launch_policy_umma_species(s->d.obs[s->cur], s->d.totals, species, blob, blob_bytes, *program, seed, draw,
-                                                 sample != 0, out_logits, out_index, (cudaStream_t)stream);
-    if (err) return fail(MBOTS_EINVAL, err);
-    CU(cudaGetLastError());
-    s->launches += 1;
-    return MBOTS_OK;
+    return policy_act_device_rows(s, species, 1, &blob, &blob_bytes, &program, seed, draw, sample, out_logits, out_index, stream);
+}
+
+extern "C" int mbots_policy_act_all(mbots_sim *s, const void *const blobs[4], const uint64_t blob_bytes[4],
+                                    const mbots_policy_program *const programs[4], uint32_t seed, uint32_t draw, int32_t sample,
+                                    float *out_logits, int32_t *out_index, void *stream)
+{
+    if (!s || !blobs || !blob_bytes || !programs) return fail(MBOTS_EINVAL, "null argument");
+    return policy_act_device_rows(s, 0, 4, blobs, blob_bytes, programs, seed, draw, sample, out_logits, out_index, stream);
 }
 
 extern "C" int mbots_policy_act(mbots_sim *s, uint32_t row_begin, uint32_t row_end, const void *blob, uint64_t blob_bytes,

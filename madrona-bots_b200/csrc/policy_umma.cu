@@ -268,38 +268,52 @@ __device__ unsigned long long g_umma_trace[5 * 2 * 2048];
 #define UTRACE(code, t, b)
 #endif
 
-struct UmmaPlan {                          /* weight blocks (32 KB each) in streaming order */
+constexpr int kUMaxNets = 4;                       /* one network per species */
+
+struct UmmaNet {                                   /* one species network: weight blocks (32 KB each) in streaming order */
+    const unsigned char *blob;
     int32_t n_blocks;
+    int32_t n_ops;
     uint32_t ofs[3 * MBOTS_POLICY_MAX_OPS];
     uint8_t op_of[3 * MBOTS_POLICY_MAX_OPS];
     uint8_t gate_of[3 * MBOTS_POLICY_MAX_OPS];
-    uint16_t bias_at[MBOTS_POLICY_MAX_OPS];   /* float offset of each op's biases in the shared-memory copy */
+    uint8_t opcode[MBOTS_POLICY_MAX_OPS];
+    uint8_t act[MBOTS_POLICY_MAX_OPS];
+    uint16_t bias_at[MBOTS_POLICY_MAX_OPS];        /* float offset of each op's biases in the shared-memory copy */
     uint16_t bias_n[MBOTS_POLICY_MAX_OPS];
+    uint32_t b_ofs[MBOTS_POLICY_MAX_OPS];
+    uint32_t row_begin, rows;                      /* the rows it acts on, unless they are resolved on the device */
+};
+
+/* What one launch does: n networks, each over its own block of rows. species0 >= 0: network j acts on the block of species
+ * species0 + j of the current row set, read from `totals` on the device. */
+struct UmmaWork {
+    int32_t n;
+    int32_t species0;
+    const Totals *totals;
+    UmmaNet net[kUMaxNets];
+};
+
+/* the launch's schedule, worked out once per CTA (shared memory): tile pairs are numbered through all networks */
+struct UmmaSched {
+    uint32_t row_begin[kUMaxNets], rows[kUMaxNets], pair_end[kUMaxNets], out_base[kUMaxNets];
+    uint32_t pairs;
 };
 
 struct UObsPtrs { const uint8_t *depth; const float *health; const float *position; const int8_t *semantic; const float *surrounding;
                   const uint32_t *owner; uint32_t worldOff; };
 
 __global__ void __launch_bounds__(kUThreads, 1)     /* 17 warps are allocated as 20: 96 registers per thread is the ceiling */
-policy_umma_kernel(UObsPtrs o, int32_t *__restrict__ action, uint32_t row_begin, uint32_t rows, const unsigned char *__restrict__ blob,
-                   mbots_policy_program prog, UmmaPlan plan, uint32_t seed, uint32_t draw, int do_sample,
-                   float *__restrict__ out_logits, int32_t *__restrict__ out_index, const Totals *__restrict__ totals, int species)
+policy_umma_kernel(UObsPtrs o, int32_t *__restrict__ action, UmmaWork work, uint32_t seed, uint32_t draw, int do_sample,
+                   float *__restrict__ out_logits, int32_t *__restrict__ out_index)
 {
-    /* totals != NULL: the rows are the block of `species` in the current row set, resolved HERE from what the last step's
-     * row scan wrote -- the host neither knows nor waits for the population; out_logits / out_index are then indexed by
-     * observation row, not by row within the block */
-    if (totals != nullptr) {
-        row_begin = 0;
-        for (int k = 0; k < species; ++k) row_begin += totals->speciesTotal[k];
-        rows = totals->speciesTotal[species];
-        if (out_logits) out_logits += (size_t)row_begin * 6;
-        if (out_index) out_index += row_begin;
-    }
     extern __shared__ unsigned char smem_raw[];
     unsigned char *smem = reinterpret_cast<unsigned char *>((reinterpret_cast<uintptr_t>(smem_raw) + 1023u) & ~(uintptr_t)1023u);
     const uint32_t smem_base = (uint32_t)__cvta_generic_to_shared(smem);
     const uint32_t w_base = smem_base, a_base = smem_base + kURing * kUBlockBytes, bar_base = a_base + 2 * kUBlockBytes;
     uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(smem + (kURing + 2) * kUBlockBytes + 128);
+    UmmaSched *sched = reinterpret_cast<UmmaSched *>(smem + (kURing + 2) * kUBlockBytes + 160);
+    static_assert(160 + sizeof(UmmaSched) <= 256, "the schedule sits between the barriers and the biases");
     /* barriers: 8 bytes each */
     auto W_FULL = [&](int i) { return bar_base + (uint32_t)i * 8u; };
     auto W_EMPTY = [&](int i) { return bar_base + 24u + (uint32_t)i * 8u; };
@@ -311,6 +325,25 @@ policy_umma_kernel(UObsPtrs o, int32_t *__restrict__ action, uint32_t row_begin,
         for (int i = 0; i < kURing; ++i) { mbar_init(W_FULL(i), 1); mbar_init(W_EMPTY(i), 1); }
         for (int t = 0; t < 2; ++t) { mbar_init(ACC_FULL(t), 1); mbar_init(A_READY(t), kUEpiWarps / 2); }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        /* the schedule: rows of every network (from the launch, or from the totals the last row scan wrote -- the host then
+         * neither knows nor waits for the population) and the tile pairs they make, numbered through all networks */
+        uint32_t first = 0, pairs = 0;
+        if (work.totals != nullptr)
+            for (int k = 0; k < work.species0; ++k) first += work.totals->speciesTotal[k];
+        for (int k = 0; k < kUMaxNets; ++k) {
+            uint32_t rb = 0, rows = 0;
+            if (k < work.n) {
+                rb = work.totals != nullptr ? first : work.net[k].row_begin;
+                rows = work.totals != nullptr ? work.totals->speciesTotal[work.species0 + k] : work.net[k].rows;
+                first += rows;
+            }
+            pairs += ((rows + kUTile - 1) / kUTile + 1) / 2;
+            sched->row_begin[k] = rb;
+            sched->rows[k] = rows;
+            sched->pair_end[k] = pairs;
+            sched->out_base[k] = work.totals != nullptr ? rb : 0u;   /* device-resolved rows: outputs indexed by observation row */
+        }
+        sched->pairs = pairs;
     }
     if (warp == kUEpiWarps) {
         asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;"
@@ -319,20 +352,17 @@ policy_umma_kernel(UObsPtrs o, int32_t *__restrict__ action, uint32_t row_begin,
     }
     float *bias_s = reinterpret_cast<float *>(smem + (kURing + 2) * kUBlockBytes + 256);
     const uint32_t bias_base = bar_base + 256u;
-    for (int i = 0; i < prog.n_ops; ++i) {
-        const float *src = reinterpret_cast<const float *>(blob + prog.ops[i].b_ofs);
-        for (int j = tid; j < plan.bias_n[i]; j += kUThreads) bias_s[plan.bias_at[i] + j] = __ldg(src + j);
-    }
+    for (int k = 0; k < work.n; ++k)
+        for (int i = 0; i < work.net[k].n_ops; ++i) {
+            const float *src = reinterpret_cast<const float *>(work.net[k].blob + work.net[k].b_ofs[i]);
+            for (int j = tid; j < work.net[k].bias_n[i]; j += kUThreads) bias_s[work.net[k].bias_at[i] + j] = __ldg(src + j);
+        }
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem = *tmem_slot;
     /* TMEM columns: tile t accumulator at t * 256, its scratch (LSTM cell / GRU helpers) at t * 256 + 128 */
-
-    const uint32_t n_tiles = (rows + kUTile - 1) / kUTile;
-    const uint32_t n_pairs = (n_tiles + 1) / 2;
-    const uint32_t my_pairs = blockIdx.x < n_pairs ? (n_pairs - blockIdx.x + gridDim.x - 1) / gridDim.x : 0;
-    const int B = plan.n_blocks;
+    const uint32_t n_pairs = sched->pairs;
 
     if (warp < kUEpiWarps) {
         /* ---------------- epilogue warps: thread = one agent row of tile t, half of its columns ---------------- */
@@ -342,11 +372,15 @@ policy_umma_kernel(UObsPtrs o, int32_t *__restrict__ action, uint32_t row_begin,
         const uint32_t acc = tmem + ((uint32_t)(w4 * 32) << 16) + (uint32_t)t * 256u, scratch = acc + 128u;
         const Key draw_key = key_split(key_init(seed), draw);
         uint32_t acc_phase = 0;
+        int k = 0;                                                           /* network of the current pair */
         UTRACE_DECL(1 + t * 2 + hf)
-        for (uint32_t it = 0; it < my_pairs; ++it) {
-            const uint32_t tile = (blockIdx.x + it * gridDim.x) * 2u + (uint32_t)t;
+        for (uint32_t p = blockIdx.x; p < n_pairs; p += gridDim.x) {
+            while (p >= sched->pair_end[k]) ++k;
+            const UmmaNet &net = work.net[k];
+            const uint32_t tile = (p - (k > 0 ? sched->pair_end[k - 1] : 0u)) * 2u + (uint32_t)t;
             const size_t lr = (size_t)tile * kUTile + r;
-            const bool live = lr < rows;
+            const bool live = lr < sched->rows[k];
+            const uint32_t row_begin = sched->row_begin[k];
             /* construct_obs of this row -> A operand (80 columns = 10 chunks; the MMA reads 5 k-steps) */
             {
                 const size_t row = (size_t)row_begin + (live ? lr : 0);
@@ -370,9 +404,9 @@ policy_umma_kernel(UObsPtrs o, int32_t *__restrict__ action, uint32_t row_begin,
                 }
 #pragma unroll
                 for (int j = 0; j < 10; ++j) {
-                    const uint4 p = make_uint4(upack_bf16(x[8 * j], x[8 * j + 1]), upack_bf16(x[8 * j + 2], x[8 * j + 3]),
-                                               upack_bf16(x[8 * j + 4], x[8 * j + 5]), upack_bf16(x[8 * j + 6], x[8 * j + 7]));
-                    if ((j >= 5) == (hf != 0)) sts128(a_tile + sw128_chunk_offset(r, (uint32_t)j), p);
+                    const uint4 pk = make_uint4(upack_bf16(x[8 * j], x[8 * j + 1]), upack_bf16(x[8 * j + 2], x[8 * j + 3]),
+                                                upack_bf16(x[8 * j + 4], x[8 * j + 5]), upack_bf16(x[8 * j + 6], x[8 * j + 7]));
+                    if ((j >= 5) == (hf != 0)) sts128(a_tile + sw128_chunk_offset(r, (uint32_t)j), pk);
                 }
             }
             fence_async_smem();
@@ -380,17 +414,17 @@ policy_umma_kernel(UObsPtrs o, int32_t *__restrict__ action, uint32_t row_begin,
             __syncwarp();
             if (lane == 0) mbar_arrive(A_READY(t));
 
+            const int B = net.n_blocks;
             for (int b = 0; b < B; ++b) {
-                const mbots_policy_op op = prog.ops[plan.op_of[b]];
-                const int gate = plan.gate_of[b];
-                const uint32_t bias = bias_base + 4u * plan.bias_at[plan.op_of[b]];
+                const int opi = net.op_of[b], opc = net.opcode[opi], gate = net.gate_of[b];
+                const uint32_t bias = bias_base + 4u * net.bias_at[opi];
                 mbar_wait(ACC_FULL(t), acc_phase);
                 acc_phase ^= 1u;
                 tc_fence_after();
                 if (lane == 0 && w4 == 0) { UTRACE(1, t, b) }
                 const int cb = hf * 64;
-                if (op.op == MBOTS_OP_LINEAR) {
-                    switch (op.act) {
+                if (opc == MBOTS_OP_LINEAR) {
+                    switch (net.act[opi]) {
                     case MBOTS_ACT_TANH: epi_block<EM_LINEAR, MBOTS_ACT_TANH>(acc, scratch, bias, bias, a_tile, r, cb); break;
                     case MBOTS_ACT_ELU: epi_block<EM_LINEAR, MBOTS_ACT_ELU>(acc, scratch, bias, bias, a_tile, r, cb); break;
                     case MBOTS_ACT_LOGSIGMOID: epi_block<EM_LINEAR, MBOTS_ACT_LOGSIGMOID>(acc, scratch, bias, bias, a_tile, r, cb); break;
@@ -399,12 +433,12 @@ policy_umma_kernel(UObsPtrs o, int32_t *__restrict__ action, uint32_t row_begin,
                     case MBOTS_ACT_SIGMOID: epi_block<EM_LINEAR, MBOTS_ACT_SIGMOID>(acc, scratch, bias, bias, a_tile, r, cb); break;
                     default: epi_block<EM_LINEAR, MBOTS_ACT_NONE>(acc, scratch, bias, bias, a_tile, r, cb); break;
                     }
-                } else if (op.op == MBOTS_OP_LSTM0) {                 /* biases: b_i, b_g, b_o */
+                } else if (opc == MBOTS_OP_LSTM0) {                   /* biases: b_i, b_g, b_o */
                     const uint32_t bg = bias + 512u * (uint32_t)gate;
                     if (gate == 0) epi_block<EM_LSTM_I, 0>(acc, scratch, bg, bg, a_tile, r, cb);
                     else if (gate == 1) epi_block<EM_LSTM_G, 0>(acc, scratch, bg, bg, a_tile, r, cb);
                     else epi_block<EM_LSTM_O, 0>(acc, scratch, bg, bg, a_tile, r, cb);
-                } else if (op.op == MBOTS_OP_GRU0) {                  /* biases: b_r, b_z, b_in, b_hn */
+                } else if (opc == MBOTS_OP_GRU0) {                    /* biases: b_r, b_z, b_in, b_hn */
                     const uint32_t bg = bias + 512u * (uint32_t)gate;
                     if (gate == 0) epi_block<EM_GRU_R, 0>(acc, scratch, bg, bias + 3u * 512u, a_tile, r, cb);
                     else if (gate == 1) epi_block<EM_GRU_Z, 0>(acc, scratch, bg, bg, a_tile, r, cb);
@@ -413,23 +447,24 @@ policy_umma_kernel(UObsPtrs o, int32_t *__restrict__ action, uint32_t row_begin,
                     uint32_t v[16];
                     if (hf == 0) { tmem_ld16(acc, v); tmem_wait_ld(v); }
                     if (live && hf == 0) {
+                        const size_t orow = (size_t)sched->out_base[k] + lr;
                         float l[6];
 #pragma unroll
-                        for (int k = 0; k < 6; ++k) l[k] = __uint_as_float(v[k]) + bias_s[plan.bias_at[plan.op_of[b]] + k];
+                        for (int q = 0; q < 6; ++q) l[q] = __uint_as_float(v[q]) + bias_s[net.bias_at[opi] + q];
                         if (out_logits) {
 #pragma unroll
-                            for (int k = 0; k < 6; ++k) out_logits[lr * 6 + k] = l[k];
+                            for (int q = 0; q < 6; ++q) out_logits[orow * 6 + q] = l[q];
                         }
                         if (do_sample) {
                             float m = l[0];
 #pragma unroll
-                            for (int k = 1; k < 6; ++k) m = fmaxf(m, l[k]);
+                            for (int q = 1; q < 6; ++q) m = fmaxf(m, l[q]);
                             float wgt[6];
 #pragma unroll
-                            for (int k = 0; k < 6; ++k) wgt[k] = __expf(l[k] - m);
+                            for (int q = 0; q < 6; ++q) wgt[q] = __expf(l[q] - m);
                             const uint32_t srow = row_begin + (uint32_t)lr;
                             const int pick = sample_and_write(wgt, draw_key, agent_id(o.owner, o.worldOff, srow), srow, action);
-                            if (out_index) out_index[lr] = pick;
+                            if (out_index) out_index[orow] = pick;
                         }
                     }
                 }
@@ -446,27 +481,31 @@ policy_umma_kernel(UObsPtrs o, int32_t *__restrict__ action, uint32_t row_begin,
     } else {
         /* ---------------- issue warp: weight ring + tcgen05.mma. Every lane runs the (warp-uniform) control flow,
          * one elected lane issues the copies, the products and the commits ---------------- */
-        const uint32_t total = my_pairs * (uint32_t)B;
-        uint32_t f_g = 0, f_b = 0, f_slot = 0;                        /* next block to fetch: number, index in the program, ring slot */
+        /* next block to fetch: pair, its network, index in that network's block list, ring slot */
+        uint32_t f_p = blockIdx.x, f_b = 0, f_slot = 0;
+        int f_k = 0;
         auto fetch = [&]() {
-            if (f_g < total) {
+            if (f_p < n_pairs) {
+                while (f_p >= sched->pair_end[f_k]) ++f_k;
                 if (elect_one()) {
                     mbar_expect_tx(W_FULL(f_slot), kUBlockBytes);
-                    bulk_copy_g2s(w_base + f_slot * kUBlockBytes, blob + plan.ofs[f_b], kUBlockBytes, W_FULL(f_slot));
+                    bulk_copy_g2s(w_base + f_slot * kUBlockBytes, work.net[f_k].blob + work.net[f_k].ofs[f_b], kUBlockBytes, W_FULL(f_slot));
                 }
-                ++f_g;
-                if (++f_b == (uint32_t)B) f_b = 0;
+                if (++f_b == (uint32_t)work.net[f_k].n_blocks) { f_b = 0; f_p += gridDim.x; }
                 if (++f_slot == (uint32_t)kURing) f_slot = 0;
             }
         };
         for (int i = 0; i < kURing; ++i) fetch();
         uint32_t a_phase = 0, slot = 0, w_phase = 0, prev_slot = 0, prev_phase = 0;
         bool first = true;
+        int k = 0;
         UTRACE_DECL(0)
-        for (uint32_t it = 0; it < my_pairs; ++it) {
+        for (uint32_t p = blockIdx.x; p < n_pairs; p += gridDim.x) {
+            while (p >= sched->pair_end[k]) ++k;
+            const int B = work.net[k].n_blocks;
             for (int b = 0; b < B; ++b) {
-                const mbots_policy_op op = prog.ops[plan.op_of[b]];
-                const uint32_t idesc = umma_idesc(op.op == MBOTS_OP_HEAD ? 16u : 128u);
+                const bool head = work.net[k].opcode[work.net[k].op_of[b]] == MBOTS_OP_HEAD;
+                const uint32_t idesc = umma_idesc(head ? 16u : 128u);
                 const uint64_t bdesc = umma_desc(w_base + slot * kUBlockBytes);
                 mbar_wait(W_FULL(slot), w_phase);
                 if (lane == 0) { UTRACE(10, 0, b) }
@@ -477,7 +516,7 @@ policy_umma_kernel(UObsPtrs o, int32_t *__restrict__ action, uint32_t row_begin,
                     tc_fence_after();
                     const uint64_t adesc = umma_desc(a_base + (uint32_t)t * kUBlockBytes);
                     if (elect_one()) {
-                        if (op.k_pad == 80u) issue_mmas<5>(tmem + (uint32_t)t * 256u, adesc, bdesc, idesc);
+                        if (b == 0) issue_mmas<5>(tmem + (uint32_t)t * 256u, adesc, bdesc, idesc);      /* the observation row: k_pad 80 */
                         else issue_mmas<8>(tmem + (uint32_t)t * 256u, adesc, bdesc, idesc);
                         umma_commit(ACC_FULL(t));
                     }
@@ -504,11 +543,15 @@ policy_umma_kernel(UObsPtrs o, int32_t *__restrict__ action, uint32_t row_begin,
     if (warp == kUEpiWarps) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"((uint32_t)kUTmemCols) : "memory");
 }
 
-/* Host: validate a SW128-layout program against the blob and derive the streaming plan. Returns 0 or a message. */
-static const char *policy_umma_plan(const mbots_policy_program &p, uint64_t blob_bytes, UmmaPlan &plan)
+/* Host: validate a SW128-layout program against the blob and derive the network's streaming plan; its biases go to
+ * [*bias_floats, ...) of the shared-memory copy. Returns 0 or a message. */
+static const char *policy_umma_plan(const mbots_policy_program &p, const void *blob, uint64_t blob_bytes, UmmaNet &net, uint32_t *bias_floats)
 {
     if (p.n_ops < 2 || p.n_ops > MBOTS_POLICY_MAX_OPS) return "program must hold 2..12 ops";
-    plan.n_blocks = 0;
+    if (reinterpret_cast<uintptr_t>(blob) & 15u) return "the blob must be 16-byte aligned";
+    net.blob = static_cast<const unsigned char *>(blob);
+    net.n_blocks = 0;
+    net.n_ops = p.n_ops;
     for (int i = 0; i < p.n_ops; ++i) {
         const mbots_policy_op &op = p.ops[i];
         const bool first = i == 0, last = i == p.n_ops - 1;
@@ -522,26 +565,26 @@ static const char *policy_umma_plan(const mbots_policy_program &p, uint64_t blob
         const uint32_t nbias = op.op == MBOTS_OP_HEAD ? 8u : op.op == MBOTS_OP_GRU0 ? 4u * 128u : blocks * 128u;
         if ((uint64_t)op.w_ofs + (uint64_t)blocks * kUBlockBytes > blob_bytes || (uint64_t)op.b_ofs + 4ull * nbias > blob_bytes)
             return "op reaches beyond the blob";
-        plan.bias_at[i] = (uint16_t)(i * 512);
-        plan.bias_n[i] = (uint16_t)nbias;
+        if (*bias_floats + nbias > (uint32_t)kUBiasFloats) return "the networks' biases exceed the kernel's shared-memory copy";
+        net.opcode[i] = (uint8_t)op.op;
+        net.act[i] = (uint8_t)op.act;
+        net.b_ofs[i] = op.b_ofs;
+        net.bias_at[i] = (uint16_t)*bias_floats;
+        net.bias_n[i] = (uint16_t)nbias;
+        *bias_floats += (nbias + 3u) & ~3u;               /* keeps every vector 16-byte aligned (ld.shared.v4) */
         for (uint32_t j = 0; j < blocks; ++j) {
-            plan.ofs[plan.n_blocks] = op.w_ofs + j * (uint32_t)kUBlockBytes;
-            plan.op_of[plan.n_blocks] = (uint8_t)i;
-            plan.gate_of[plan.n_blocks] = (uint8_t)j;
-            ++plan.n_blocks;
+            net.ofs[net.n_blocks] = op.w_ofs + j * (uint32_t)kUBlockBytes;
+            net.op_of[net.n_blocks] = (uint8_t)i;
+            net.gate_of[net.n_blocks] = (uint8_t)j;
+            ++net.n_blocks;
         }
     }
     return nullptr;
 }
 
-static const char *launch_umma(const ObsSet &o, const Totals *totals, int species, uint32_t row_begin, uint32_t rows, const void *blob,
-                               uint64_t blob_bytes, const mbots_policy_program &prog, uint32_t seed, uint32_t draw, int do_sample,
+static const char *launch_umma(const ObsSet &o, UmmaWork &work, uint32_t pairs_known, uint32_t seed, uint32_t draw, int do_sample,
                                float *out_logits, int32_t *out_index, cudaStream_t s)
 {
-    UmmaPlan plan = {};
-    const char *err = policy_umma_plan(prog, blob_bytes, plan);
-    if (err || (rows == 0 && totals == nullptr)) return err;
-    if (reinterpret_cast<uintptr_t>(blob) & 15u) return "the blob must be 16-byte aligned";
     int dev = 0, sms = 148;
     cudaGetDevice(&dev);
     static bool attr_set[64] = {};                      /* the opt-in is per device */
@@ -550,13 +593,11 @@ static const char *launch_umma(const ObsSet &o, const Totals *totals, int specie
             return "cudaFuncSetAttribute(MaxDynamicSharedMemorySize) failed";
         attr_set[dev] = true;
     }
-    const uint32_t pairs = ((rows + kUTile - 1) / kUTile + 1) / 2;
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-    /* persistent: one CTA per SM (all of them when the row count is only known on the device) */
-    const uint32_t grid = totals == nullptr && pairs < (uint32_t)sms ? pairs : (uint32_t)sms;
+    /* persistent: one CTA per SM (all of them when the row counts are only known on the device) */
+    const uint32_t grid = work.totals == nullptr && pairs_known < (uint32_t)sms ? pairs_known : (uint32_t)sms;
     const UObsPtrs ptrs = {o.depth, o.health, o.position, o.semantic, o.surrounding, o.owner, o.worldIdOffset};
-    policy_umma_kernel<<<grid, kUThreads, kUSmemBytes, s>>>(ptrs, o.action, row_begin, rows, static_cast<const unsigned char *>(blob),
-                                                            prog, plan, seed, draw, do_sample, out_logits, out_index, totals, species);
+    policy_umma_kernel<<<grid, kUThreads, kUSmemBytes, s>>>(ptrs, o.action, work, seed, draw, do_sample, out_logits, out_index);
     return nullptr;
 }
 
@@ -564,15 +605,35 @@ const char *launch_policy_umma(const ObsSet &o, uint32_t row_begin, uint32_t row
                                const mbots_policy_program &prog, uint32_t seed, uint32_t draw, int do_sample,
                                float *out_logits, int32_t *out_index, cudaStream_t s)
 {
-    return launch_umma(o, nullptr, 0, row_begin, rows, blob, blob_bytes, prog, seed, draw, do_sample, out_logits, out_index, s);
+    UmmaWork work = {};
+    uint32_t bias_floats = 0;
+    const char *err = policy_umma_plan(prog, blob, blob_bytes, work.net[0], &bias_floats);
+    if (err || rows == 0) return err;
+    work.n = 1;
+    work.species0 = -1;
+    work.totals = nullptr;
+    work.net[0].row_begin = row_begin;
+    work.net[0].rows = rows;
+    return launch_umma(o, work, ((rows + kUTile - 1) / kUTile + 1) / 2, seed, draw, do_sample, out_logits, out_index, s);
 }
 
-/* the block of one species (0..3) of the current row set, row range resolved on the device from `totals` */
-const char *launch_policy_umma_species(const ObsSet &o, const Totals *totals, int species, const void *blob, uint64_t blob_bytes,
-                                       const mbots_policy_program &prog, uint32_t seed, uint32_t draw, int do_sample,
-                                       float *out_logits, int32_t *out_index, cudaStream_t s)
+/* `n` networks for the blocks of species species0 .. species0 + n - 1 of the current row set, the row ranges resolved on the
+ * device from `totals`: ONE launch (n = 4: every agent of the simulator acts) */
+const char *launch_policy_umma_species(const ObsSet &o, const Totals *totals, int species0, int n, const void *const *blobs,
+                                       const uint64_t *blob_bytes, const mbots_policy_program *const *progs, uint32_t seed,
+                                       uint32_t draw, int do_sample, float *out_logits, int32_t *out_index, cudaStream_t s)
 {
-    return launch_umma(o, totals, species, 0, 0, blob, blob_bytes, prog, seed, draw, do_sample, out_logits, out_index, s);
+    if (n < 1 || species0 < 0 || species0 + n > kUMaxNets) return "species range outside 0..3";
+    UmmaWork work = {};
+    uint32_t bias_floats = 0;
+    for (int k = 0; k < n; ++k) {
+        const char *err = policy_umma_plan(*progs[k], blobs[k], blob_bytes[k], work.net[k], &bias_floats);
+        if (err) return err;
+    }
+    work.n = n;
+    work.species0 = species0;
+    work.totals = totals;
+    return launch_umma(o, work, 0, seed, draw, do_sample, out_logits, out_index, s);
 }
 
 } // namespace mbk

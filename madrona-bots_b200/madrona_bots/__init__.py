@@ -310,6 +310,18 @@ class SimManager:
             ctypes.c_void_p(out_index.data_ptr()) if out_index is not None else None, self._stream()),
             "mbots_policy_act_species")
 
+    def policy_act_all(self, fused4, seed, draw, sample=True, out_index=None, out_logits=None):
+        """All four species in ONE kernel launch (`fused4`: four FusedPolicy in the sw128 layout, species order), row
+        ranges resolved on the device: no host wait. Outputs as in `policy_act_species`."""
+        blobs = (ctypes.c_void_p * 4)(*[f.blob.data_ptr() for f in fused4])
+        sizes = (ctypes.c_uint64 * 4)(*[f.blob.numel() for f in fused4])
+        progs = (ctypes.POINTER(_native.PolicyProgram) * 4)(*[ctypes.pointer(f.program) for f in fused4])
+        _native.check(self._lib.mbots_policy_act_all(
+            self._h, blobs, sizes, progs, int(seed) & 0xFFFFFFFF, int(draw) & 0xFFFFFFFF, 1 if sample else 0,
+            ctypes.c_void_p(out_logits.data_ptr()) if out_logits is not None else None,
+            ctypes.c_void_p(out_index.data_ptr()) if out_index is not None else None, self._stream()),
+            "mbots_policy_act_all")
+
     # ---- state checkpoint / restore (SURVEY section 8(f) item 3) ---------------------------
     def save_state(self, path=None):
         """Every persistent array of the simulator as one uint8 numpy blob (also written to `path`

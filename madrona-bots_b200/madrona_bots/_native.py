@@ -26,7 +26,7 @@ SYMBOLS = [
     "mbots_episode_stats", "mbots_launch_count", "mbots_profile", "mbots_profile_read",
     "mbots_row_capacity", "mbots_pack_observations", "mbots_sample_actions", "mbots_policy_act", "mbots_state_bytes", "mbots_save_state", "mbots_load_state",
     "mbots_rollout_step_async", "mbots_write_actions", "mbots_graph_launch_count", "mbots_debug_stale_views", "mbots_species_blocks",
-    "mbots_row_scan_static", "mbots_policy_act_species", "mbots_last_error", "mbots_version",
+    "mbots_row_scan_static", "mbots_policy_act_species", "mbots_policy_act_all", "mbots_last_error", "mbots_version",
 ]
 
 
@@ -89,6 +89,8 @@ def lib():
     L.mbots_sample_actions.argtypes = [vp, u32, u32, vp, u32, u32, vp, vp]
     L.mbots_policy_act.argtypes = [vp, u32, u32, vp, u64, ctypes.POINTER(PolicyProgram), u32, u32, i32, vp, vp, vp]
     L.mbots_policy_act_species.argtypes = [vp, i32, vp, u64, ctypes.POINTER(PolicyProgram), u32, u32, i32, vp, vp, vp]
+    L.mbots_policy_act_all.argtypes = [vp, ctypes.POINTER(vp), ctypes.POINTER(u64), ctypes.POINTER(ctypes.POINTER(PolicyProgram)), u32, u32,
+                                       i32, vp, vp, vp]
     L.mbots_row_capacity.argtypes = [vp, ctypes.POINTER(u64)]
     L.mbots_state_bytes.argtypes = [vp, ctypes.POINTER(u64)]
     L.mbots_save_state.argtypes = [vp, vp, u64, vp]

@@ -335,12 +335,16 @@ class PolicyRunner:
         self.draw += 1
         return picked
 
-    def act_async(self, out_index=None, out_logits=None):
-        """act() without any host wait: four kernels whose row ranges are resolved on the device (fused SW128 policies
-        only). With `sim.rollout_step_async(None, shift=True)` after it, a whole rollout step -- act, step, sensor, shift
-        -- is five launches and the host may run several steps ahead; same draws as act(), so the same rollout."""
+    def act_async(self, out_index=None, out_logits=None, one_launch=True):
+        """act() without any host wait: ONE kernel for the four species (or four with one_launch=False) whose row ranges
+        are resolved on the device (fused SW128 policies only). With `sim.rollout_step_async(None, shift=True)` after it, a
+        whole rollout step -- act, step, sensor, shift -- is two launches and the host may run several steps ahead; same
+        draws as act(), so the same rollout."""
         if self.fused is None:
             raise ValueError("act_async needs fused policies (PolicyRunner(..., fused='sw128'))")
-        for k in range(4):
-            self.sim.policy_act_species(k, self.fused[k], self.seed, self.draw, out_index=out_index, out_logits=out_logits)
+        if one_launch:
+            self.sim.policy_act_all(self.fused, self.seed, self.draw, out_index=out_index, out_logits=out_logits)
+        else:
+            for k in range(4):
+                self.sim.policy_act_species(k, self.fused[k], self.seed, self.draw, out_index=out_index, out_logits=out_logits)
         self.draw += 1

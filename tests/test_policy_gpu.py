@@ -378,8 +378,10 @@ def test_sampled_actions_do_not_depend_on_the_sharding(cuda_device):
     assert st[10] > 0 or st[11] > 0 or st[15] > 0, "the policy must have done something"
 
 
-def test_act_async_rollout_equals_the_blocking_loop(cuda_device):
-    """mbots_policy_act_species: the acting kernels take their row ranges from the device, so act + step + sensor + shift
+@pytest.mark.parametrize("one_launch", [True, False])
+def test_act_async_rollout_equals_the_blocking_loop(cuda_device, one_launch):
+    """mbots_policy_act_all (one launch for the four species) / mbots_policy_act_species (one per species): the acting
+    kernels take their row ranges from the device, so act + step + sensor + shift
     can be enqueued steps ahead with no host wait. Same draws, same rows: the rollout must equal the blocking loop
     (step, act through species_blocks(), shift) on every export, and the indices / logits it reports (by observation row)
     must be the blocking call's."""
@@ -403,7 +405,7 @@ def test_act_async_rollout_equals_the_blocking_loop(cuda_device):
         a.step()
         a.shift_observations()
         last = t == steps - 1
-        rb.act_async(out_index=idx if last else None, out_logits=lg if last else None)   # nothing waits for anything
+        rb.act_async(out_index=idx if last else None, out_logits=lg if last else None, one_launch=one_launch)   # no host wait
         b.rollout_step_async(None, shift=True)
         if last:
             b.sync()
