@@ -31,6 +31,7 @@ t0 = int(ev[order[0], 1])
 names = {1: "epi wake", 3: "epi math done", 5: "epi fenced", 10: "iss w_full", 11: "iss a_ready", 12: "iss issued", 13: "iss w_empty"}
 who = ["issuer", "epi t0 h0", "epi t0 h1", "epi t1 h0", "epi t1 h1"]
 print("agents", A, "events", len(ev))
-for i in order[:int(sys.argv[2]) if len(sys.argv) > 2 else 300]:
+first = int(sys.argv[3]) if len(sys.argv) > 3 else 0          # skip the ramp: a window of the steady state
+for i in order[first:first + (int(sys.argv[2]) if len(sys.argv) > 2 else 300)]:
     code = int(ev[i, 0]) & 0x7fffffff
     print(f"{int(ev[i, 1]) - t0:9d}  {who[actor[i]]:10s} tile {(code >> 8) & 255} block {code >> 16:2d}  {names.get(code & 255, code & 255)}")
