@@ -342,8 +342,14 @@ class PolicyRunner:
         draws as act(), so the same rollout."""
         if self.fused is None:
             raise ValueError("act_async needs fused policies (PolicyRunner(..., fused='sw128'))")
-        if one_launch:
-            self.sim.policy_act_all(self.fused, self.seed, self.draw, out_index=out_index, out_logits=out_logits)
+        if one_launch and not getattr(self, "_too_big_for_one_launch", False):
+            try:
+                self.sim.policy_act_all(self.fused, self.seed, self.draw, out_index=out_index, out_logits=out_logits)
+            except RuntimeError as e:
+                if "biases exceed" not in str(e):
+                    raise
+                self._too_big_for_one_launch = True       # four deep networks: one launch per species from now on
+                return self.act_async(out_index, out_logits, one_launch=False)
         else:
             for k in range(4):
                 self.sim.policy_act_species(k, self.fused[k], self.seed, self.draw, out_index=out_index, out_logits=out_logits)
