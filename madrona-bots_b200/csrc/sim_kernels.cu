@@ -1022,9 +1022,12 @@ __device__ __forceinline__ void export_world(const SimDev &d, int cur, int with_
         };
 
         int cqn = 0;                                    /* pairs that passed stage 1, warp-uniform, < 32 between iterations */
-        for (int sub0 = 0; sub0 < m; sub0 += 32) {
-            const int ms = min(32, m - sub0);
-            const int lg = ms > 16 ? 5 : ms > 8 ? 4 : ms > 4 ? 3 : ms > 2 ? 2 : ms > 1 ? 1 : 0;   /* 1 << lg >= ms */
+        for (int sub0 = 0, ms = 0; sub0 < m; sub0 += ms) {
+            /* a block of 2^lg observers costs 2^lg / 32 of a full one whatever part of it is occupied: take 16 (or 8) and leave
+             * the rest to the next block rather than round 17-27 (9-13) observers up -- half a world is 16-20 observers */
+            const int rem = m - sub0;
+            const int lg = rem >= 28 ? 5 : rem >= 14 ? 4 : rem > 4 ? 3 : rem > 2 ? 2 : rem > 1 ? 1 : 0;
+            ms = min(1 << lg, rem);
             const int il = lane & ((1 << lg) - 1), jl = lane >> lg, tpi = 32 >> lg;
             const bool on_i = il < ms;
             const int ol = sub0 + (on_i ? il : 0);      /* observer within the tile */
