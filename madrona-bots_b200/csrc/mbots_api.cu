@@ -32,6 +32,8 @@ static int fail(int code, const char *what, cudaError_t ce = cudaSuccess)
     return code;
 }
 
+namespace mbk { bool shift_bulk_enabled(); void launch_shift_bulk(const SimDev &d, int cur, cudaStream_t s); }   /* shift_bulk.cu */
+
 /* row_scan_static.cu reports through the same mbots_last_error() */
 namespace mbk { int set_error(int code, const char *what, cudaError_t ce) { return fail(code, what, ce); } }
 
@@ -527,7 +529,8 @@ int mbots_shift_observations_async(mbots_sim *s, void *stream)
     cudaStream_t st = (cudaStream_t)stream;
     if (s->profile) { resolve_shift_timing(s); cudaEventRecord(s->evShift[0], st); }
     /* grid sized from the capacity bound when the host count is stale */
-    launch_shift(s->d, s->cur, s->dirty ? s->d.numWorlds * s->d.cap : s->totalAgents, st);
+    if (mbk::shift_bulk_enabled()) mbk::launch_shift_bulk(s->d, s->cur, st);
+    else launch_shift(s->d, s->cur, s->dirty ? s->d.numWorlds * s->d.cap : s->totalAgents, st);
     if (s->profile) { cudaEventRecord(s->evShift[1], st); s->shiftPending = true; }
     CU(cudaGetLastError());
     s->launches += 1;
