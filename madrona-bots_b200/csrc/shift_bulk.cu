@@ -110,6 +110,9 @@ __global__ void __launch_bounds__(kBulkThreads) shift_bulk_kernel(BulkPlan plan,
                 sb_store(plan.col[c].dst + off, smem0 + st * kBulkChunk, bytes);
             }
         }
+        /* the other threads only work on stats tiles, but must not drift from the issuing thread: a parity wait answers for the
+         * phase before the current one too, so a thread two uses of a stage ahead would patch whatever tile is in it */
+        __syncthreads();
     }
     if (tid == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
     /* tails below 16 bytes (columns whose length is not a multiple of 16) */

@@ -442,3 +442,31 @@ def test_write_through_a_stale_view_is_detected(cuda_device):
     o, g = make_pair(16, 3, 32)                          # and the mode does not change results
     g.debug_stale_views(True)
     drive(o, g, steps=12, seed=1, mode="bits")
+
+
+def test_bulk_copy_shift_equals_the_columns_it_copies(cuda_device):
+    """shift_observations() runs on the bulk-copy engine (csrc/shift_bulk.cu): 16 KB tiles through a four-stage shared-memory
+    ring per CTA. At 12,000 worlds every CTA takes ~8 tiles, so the ring and the mbarrier phases wrap (the small oracle cases
+    take one or two tiles per CTA); an odd row count leaves 8- and 4-byte tails behind the 16-byte bulk part. prev := cur on
+    every column, with the reference's stats field mix-up (U7)."""
+    import torch
+    from madrona_bots import SimManager
+    sim = SimManager(0, 12000, 3, 32)
+    rng = np.random.default_rng(1)
+    for t in range(3):
+        A = sim.num_agents()
+        sim.action_tensor(False).to_torch().copy_(torch.from_numpy(rng.integers(0, 2, (A, 6)).astype(np.int32)))
+        sim.hidden_state_tensor(False).to_torch().copy_(torch.from_numpy(rng.standard_normal((A, 16)).astype(np.float32)))
+        sim.step()
+        cur = {n: gpu_np(sim, n).copy() for n in ("HIDDEN_STATE", "ACTION", "STATS", "POSITION", "SURROUNDING", "HEALTH", "REWARD")}
+        untouched = {n: gpu_np(sim, n).copy() for n in ("PREV_SENSOR_DEPTH", "PREV_SENSOR_SEMANTIC", "SENSOR_DEPTH")}
+        sim.shift_observations()
+        for n, v in cur.items():
+            want = v.copy()
+            if n == "STATS":
+                want[:, 1] = v[:, 0]
+            np.testing.assert_array_equal(gpu_np(sim, "PREV_" + n), want, err_msg=f"step {t}: PREV_{n}")
+            np.testing.assert_array_equal(gpu_np(sim, n), v, err_msg=f"step {t}: {n} changed")
+        for n, v in untouched.items():
+            np.testing.assert_array_equal(gpu_np(sim, n), v, err_msg=f"step {t}: {n} changed")
+    assert sim.num_agents() * 132 > 444 * 5 * 16384, "too few tiles per CTA to wrap the ring"
