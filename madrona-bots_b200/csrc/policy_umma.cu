@@ -507,6 +507,15 @@ policy_umma_kernel(UObsPtrs o, int32_t *__restrict__ action, UmmaWork work, uint
                 const bool head = work.net[k].opcode[work.net[k].op_of[b]] == MBOTS_OP_HEAD;
                 const uint32_t idesc = umma_idesc(head ? 16u : 128u);
                 const uint64_t bdesc = umma_desc(w_base + slot * kUBlockBytes);
+                if (!first) {
+                    /* The products of the previous block are done about now (they were issued at the end of the last
+                     * iteration): refill its slot at once, before this warp goes to sleep on the tiles' operands. A weight
+                     * block takes ~5,500 cycles to land; refilling after this block's products instead left it one block
+                     * period less (r4s: acting kernel -1.3 %). */
+                    mbar_wait(W_EMPTY(prev_slot), prev_phase);
+                    if (lane == 0) { UTRACE(13, 0, b) }
+                    fetch();
+                }
                 mbar_wait(W_FULL(slot), w_phase);
                 if (lane == 0) { UTRACE(10, 0, b) }
 #pragma unroll
@@ -526,11 +535,6 @@ policy_umma_kernel(UObsPtrs o, int32_t *__restrict__ action, UmmaWork work, uint
                 a_phase ^= 1u;
                 if (elect_one()) umma_commit(W_EMPTY(slot));
                 __syncwarp();
-                if (!first) {              /* the slot of the previous block is free once its products are done: refill it */
-                    mbar_wait(W_EMPTY(prev_slot), prev_phase);
-                    if (lane == 0) { UTRACE(13, 0, b) }
-                    fetch();
-                }
                 first = false;
                 prev_slot = slot;
                 prev_phase = w_phase;
